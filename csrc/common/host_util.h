@@ -1,0 +1,34 @@
+// Host-side helpers shared by every translation unit of libdtm_b200: error reporting through the
+// C ABI (integer status + thread-local message) and the lazily resolved driver entry points.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dtm {
+
+// Records `msg` as the calling thread's last error and returns a non-zero status.
+int dtm_fail(const char* msg);
+int dtm_fail_cuda(cudaError_t e, const char* expr, const char* file, int line);
+
+#define DTM_CUDA_OK(expr)                                                        \
+  do {                                                                           \
+    cudaError_t _e = (expr);                                                     \
+    if (_e != cudaSuccess) return ::dtm::dtm_fail_cuda(_e, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+// cuTensorMapEncodeTiled resolved through cudaGetDriverEntryPoint, so the library carries no link-time
+// dependency on libcuda.so and can be dlopen'ed on a machine without a driver (build checks, CPU CI).
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+PFN_encodeTiled get_encode_tiled();
+
+// 2-D bf16 row-major tensor [outer][inner] (inner contiguous), box {box_inner, box_outer}.
+// swizzle_bytes in {0, 32, 64, 128}. Out-of-bounds elements read as zero.
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_stride_bytes,
+                      uint32_t box_inner, uint32_t box_outer, uint32_t swizzle_bytes);
+
+int device_sm_count();
+
+}  // namespace dtm

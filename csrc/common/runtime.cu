@@ -1,0 +1,91 @@
+// Runtime glue of libdtm_b200: error strings, device queries, TMA tensor-map construction.
+#include "host_util.h"
+#include "../../include/dtm_b200.h"
+#include <mutex>
+#include <stdio.h>
+#include <string.h>
+
+namespace dtm {
+
+static thread_local char g_last_error[512] = "";
+
+int dtm_fail(const char* msg) {
+  snprintf(g_last_error, sizeof(g_last_error), "%s", msg);
+  return 1;
+}
+
+int dtm_fail_cuda(cudaError_t e, const char* expr, const char* file, int line) {
+  snprintf(g_last_error, sizeof(g_last_error), "CUDA error %d (%s) in `%s` at %s:%d", (int)e, cudaGetErrorString(e),
+           expr, file, line);
+  return 2;
+}
+
+PFN_encodeTiled get_encode_tiled() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_stride_bytes,
+                      uint32_t box_inner, uint32_t box_outer, uint32_t swizzle_bytes) {
+  PFN_encodeTiled enc = get_encode_tiled();
+  if (!enc) return dtm_fail("cuTensorMapEncodeTiled is not available (no CUDA driver?)");
+  if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return dtm_fail("TMA base pointer must be 16-byte aligned");
+  if (row_stride_bytes % 16 != 0) return dtm_fail("TMA row stride must be a multiple of 16 bytes");
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {row_stride_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMapSwizzle sw = CU_TENSOR_MAP_SWIZZLE_NONE;
+  if (swizzle_bytes == 32) sw = CU_TENSOR_MAP_SWIZZLE_32B;
+  else if (swizzle_bytes == 64) sw = CU_TENSOR_MAP_SWIZZLE_64B;
+  else if (swizzle_bytes == 128) sw = CU_TENSOR_MAP_SWIZZLE_128B;
+  else if (swizzle_bytes != 0) return dtm_fail("unsupported TMA swizzle");
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[160];
+    snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled failed with CUresult %d (inner=%llu outer=%llu box=%ux%u)", (int)r,
+             (unsigned long long)inner, (unsigned long long)outer, box_inner, box_outer);
+    return dtm_fail(buf);
+  }
+  return 0;
+}
+
+int device_sm_count() {
+  static int cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+}  // namespace dtm
+
+extern "C" const char* dtm_last_error(void) { return dtm::g_last_error; }
+
+extern "C" int dtm_abi_version(void) { return DTM_ABI_VERSION; }
+
+extern "C" int dtm_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin) {
+  int dev = 0;
+  DTM_CUDA_OK(cudaGetDevice(&dev));
+  cudaDeviceProp p;
+  DTM_CUDA_OK(cudaGetDeviceProperties(&p, dev));
+  if (sm_count) *sm_count = p.multiProcessorCount;
+  if (cc_major) *cc_major = p.major;
+  if (cc_minor) *cc_minor = p.minor;
+  if (smem_optin) *smem_optin = p.sharedMemPerBlockOptin;
+  return 0;
+}
