@@ -1,0 +1,214 @@
+// conv2 input gradient on tcgen05 (autodiff of mnist_input.py:161): dP1 = dZ2 (*) flip(W2), fused with the backward
+// of what precedes conv2 in the graph — ReLU mask of conv1's pooled output, or LRN backward + ReLU mask for the
+// `reference` preset (mnist_input.py:149-153).
+//
+// Same zero-copy-tap scheme as the forward kernel: dZ2 arrives in the plane layout (64 channels = 8 planes,
+// 32 KiB per image, one bulk copy), every tap is a re-based descriptor.  Per image 2 M-tiles x 25 taps x 4
+// K-chunks = 200 tcgen05.mma of shape 128 x 32 x 16.  The B operand is W2 with both spatial axes flipped and
+// (ci, co) swapped: B[k = tap'*64 + co][n = ci] = W2[24 - tap'][ci][co]; eight consecutive co are contiguous in
+// the TensorFlow layout, so the re-pack into [k/8][n][8] is one 16-byte load per chunk.
+#include "../common/ptx.cuh"
+#include "../common/host_util.h"
+#include "../../include/dtm_b200.h"
+#include "plane_layout.cuh"
+
+namespace dtm {
+
+constexpr int DG_CI = 32;                                // output channels of this GEMM (conv2's input channels)
+constexpr int DG_CO = 64;                                // reduction channels per tap
+constexpr int DG_K = 25 * DG_CO;                         // 1600
+constexpr int DG_W_BYTES = DG_K * DG_CI * 2;             // 102400
+constexpr int DG_IMG_BYTES = plane_image_bytes(DG_CO);   // 32768
+constexpr int DG_BUFS = 2;
+constexpr int DG_SMEM = DG_W_BYTES + PL_GUARD_BYTES + DG_BUFS * DG_IMG_BYTES + PL_GUARD_BYTES + 128;
+
+template <bool LRN>
+__global__ void __launch_bounds__(256, 1)
+conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* __restrict__ w2,
+                   const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ pool_raw, int batch,
+                   __nv_bfloat16* __restrict__ dpool1) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t img_full[DG_BUFS], img_empty[DG_BUFS], acc_full[2], acc_empty[2];
+  __shared__ uint32_t tmem_slot;
+
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  uint8_t* s_w = smem;                                   // [k8 = 200][n = 32][8] bf16
+  uint8_t* s_guard = smem + DG_W_BYTES;
+  uint8_t* s_img = s_guard + PL_GUARD_BYTES;
+
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t lane = lane_id();
+
+  if (warp == 1 && elect_one()) {
+    for (int i = 0; i < DG_BUFS; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+    fence_mbar_init();
+  }
+  if (warp == 2) { tmem_alloc(&tmem_slot, 128); tmem_relinquish(); }
+  {
+    uint4 z = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x * 16; i < 2 * PL_GUARD_BYTES + DG_BUFS * DG_IMG_BYTES; i += blockDim.x * 16)
+      *reinterpret_cast<uint4*>(s_guard + i) = z;
+  }
+  for (int chunk = threadIdx.x; chunk < (DG_K / 8) * DG_CI; chunk += blockDim.x) {
+    const int k8 = chunk / DG_CI, ci = chunk % DG_CI;
+    const int tap_f = k8 >> 3, co8 = k8 & 7;
+    const uint4 v = *reinterpret_cast<const uint4*>(w2 + ((24 - tap_f) * DG_CI + ci) * DG_CO + co8 * 8);
+    *reinterpret_cast<uint4*>(s_w + chunk * 16) = v;
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int first = blockIdx.x, stride = gridDim.x;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int it = 0;
+      for (int img = first; img < batch; img += stride, ++it) {
+        const int b = it % DG_BUFS;
+        mbar_wait(&img_empty[b], ((it / DG_BUFS) & 1) ^ 1, 20);
+        mbar_arrive_expect_tx(&img_full[b], DG_IMG_BYTES);
+        bulk_load_1d(s_img + b * DG_IMG_BYTES, dz2_planes + static_cast<size_t>(img) * DG_IMG_BYTES, DG_IMG_BYTES, &img_full[b]);
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, DG_CI, false, false);
+      const uint32_t w_base = smem_u32(s_w);
+      int it = 0;
+      for (int img = first; img < batch; img += stride, ++it) {
+        const int b = it % DG_BUFS;
+        const int a = it & 1;
+        mbar_wait(&acc_empty[a], ((it >> 1) & 1) ^ 1, 21);
+        mbar_wait(&img_full[b], (it / DG_BUFS) & 1, 22);
+        tc_fence_after();
+        const uint32_t img_base = smem_u32(s_img + b * DG_IMG_BYTES);
+#pragma unroll 1
+        for (int t = 0; t < 2; ++t) {
+          const uint32_t d_tmem = tmem_base + a * 64 + t * 32;
+#pragma unroll 1
+          for (int tap = 0; tap < 25; ++tap) {
+            const int kh = tap / 5, kw = tap % 5;
+            const uint32_t a_addr = img_base + (t * 128 + kh * PL_GRID + kw - 2) * 16;
+            const uint32_t b_addr = w_base + tap * 8 * (DG_CI * 16);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint64_t da = umma_smem_desc(a_addr + j * 2 * PL_PLANE_BYTES, PL_PLANE_BYTES, 128, UMMA_SWIZZLE_NONE);
+              const uint64_t db = umma_smem_desc(b_addr + j * 2 * (DG_CI * 16), DG_CI * 16, 128, UMMA_SWIZZLE_NONE);
+              umma_f16(d_tmem, da, db, idesc, (tap | j) ? 1u : 0u);
+            }
+          }
+        }
+        umma_commit(&img_empty[b]);
+        umma_commit(&acc_full[a]);
+      }
+    }
+  } else if (warp >= 4) {
+    const uint32_t q = warp & 3;
+    const int w_px = lane & 15, h_sub = lane >> 4;
+    int it = 0;
+    for (int img = first; img < batch; img += stride, ++it) {
+      const int a = it & 1;
+      mbar_wait(&acc_full[a], (it >> 1) & 1, 23);
+      tc_fence_after();
+#pragma unroll 1
+      for (int t = 0; t < 2; ++t) {
+        const int h = t * 8 + q * 2 + h_sub;
+        const bool valid = h < IMG && w_px < IMG;
+        uint32_t r[32];
+        tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 64 + t * 32, r);
+        tmem_ld_wait();
+        if (!valid) continue;
+        float g[DG_CI];
+#pragma unroll
+        for (int j = 0; j < DG_CI; ++j) g[j] = __uint_as_float(r[j]);
+        float act[DG_CI];  // the activation whose sign gates the gradient (pooled conv1 output, pre-LRN)
+        if (LRN) {
+          const uint4* src = reinterpret_cast<const uint4*>(pool_raw + (static_cast<size_t>(img) * (IMG * IMG) + h * IMG + w_px) * DG_CI);
+#pragma unroll
+          for (int c8 = 0; c8 < 4; ++c8) {
+            const uint4 u = src[c8];
+            const uint32_t wds[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { act[c8 * 8 + 2 * i] = bf16_lo(wds[i]); act[c8 * 8 + 2 * i + 1] = bf16_hi(wds[i]); }
+          }
+          // LRN backward (TF semantics): s_c = 1 + alpha*sum a^2 ; y_c = a_c s_c^-beta
+          //   da_j = dy_j s_j^-beta - 2 alpha beta a_j * sum_{|c-j|<=4} dy_c a_c s_c^(-beta-1)
+          const float alpha = 0.001f / 9.0f, beta = 0.75f;
+          float t1[DG_CI], sp[DG_CI];
+#pragma unroll
+          for (int c = 0; c < DG_CI; ++c) {
+            float s = 0.0f;
+#pragma unroll
+            for (int d = -4; d <= 4; ++d)
+              if (c + d >= 0 && c + d < DG_CI) s += act[c + d] * act[c + d];
+            s = 1.0f + alpha * s;
+            const float p = __powf(s, -beta);
+            sp[c] = p;
+            t1[c] = g[c] * act[c] * p / s;
+          }
+#pragma unroll
+          for (int j = 0; j < DG_CI; ++j) {
+            float acc = 0.0f;
+#pragma unroll
+            for (int d = -4; d <= 4; ++d)
+              if (j + d >= 0 && j + d < DG_CI) acc += t1[j + d];
+            g[j] = g[j] * sp[j] - 2.0f * alpha * beta * act[j] * acc;
+          }
+        } else {
+          const uint8_t* src = p1_planes + static_cast<size_t>(img) * plane_image_bytes(DG_CI);
+#pragma unroll
+          for (int c8 = 0; c8 < 4; ++c8) {
+            const uint4 u = *reinterpret_cast<const uint4*>(src + plane_offset(h, w_px, c8 * 8));
+            const uint32_t wds[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { act[c8 * 8 + 2 * i] = bf16_lo(wds[i]); act[c8 * 8 + 2 * i + 1] = bf16_hi(wds[i]); }
+          }
+        }
+        uint4* dst = reinterpret_cast<uint4*>(dpool1 + (static_cast<size_t>(img) * (IMG * IMG) + h * IMG + w_px) * DG_CI);
+#pragma unroll
+        for (int c8 = 0; c8 < 4; ++c8) {
+          float o[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o[i] = act[c8 * 8 + i] > 0.0f ? g[c8 * 8 + i] : 0.0f;
+          dst[c8] = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[a]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 128);
+}
+
+}  // namespace dtm
+
+extern "C" int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, const void* p1_planes, const void* pool_raw,
+                               int batch, int lrn, void* dpool1, void* stream) {
+  using namespace dtm;
+  if (batch <= 0) return dtm_fail("conv2_dgrad: batch must be positive");
+  if (lrn && !pool_raw) return dtm_fail("conv2_dgrad: LRN backward needs pool_raw");
+  if (!lrn && !p1_planes) return dtm_fail("conv2_dgrad: needs the conv1 activation for the ReLU mask");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  static bool configured = false;
+  if (!configured) {
+    DTM_CUDA_OK(cudaFuncSetAttribute(conv2_dgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
+    DTM_CUDA_OK(cudaFuncSetAttribute(conv2_dgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
+    configured = true;
+  }
+  const int grid = min(batch, device_sm_count());
+  auto launch = [&](auto kern) {
+    kern<<<grid, 256, DG_SMEM, s>>>(static_cast<const uint8_t*>(dz2_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
+                                    static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(pool_raw), batch,
+                                    static_cast<__nv_bfloat16*>(dpool1));
+  };
+  if (lrn) launch(conv2_dgrad_kernel<true>);
+  else     launch(conv2_dgrad_kernel<false>);
+  DTM_CUDA_OK(cudaGetLastError());
+  return 0;
+}

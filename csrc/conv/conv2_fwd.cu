@@ -1,0 +1,244 @@
+// conv2 forward on tcgen05: 5x5 SAME conv (32 -> 64) + bias + ReLU [+ LRN] + 2x2 max-pool, one persistent kernel.
+// Reference graph: mnist_input.py:156-172 (65 % of the model's forward FLOPs).
+//
+// Implicit GEMM without im2col.  The pooled conv1 activation arrives in the plane layout (plane_layout.cuh):
+// one cp.async.bulk drops a whole 16 KiB image into shared memory, and each of the 25 filter taps is the *same*
+// bytes seen through a UMMA descriptor whose start address is moved by (kh*16 + kw - 2) pixels.  Per image:
+//   2 M-tiles (image rows 0-7 / 8-15 of the 16-wide grid) x 25 taps x 2 K-chunks = 100 tcgen05.mma (128x64x16),
+// accumulating into a 128-column TMEM window that is double buffered against the epilogue.  The 100 KiB of
+// filter weights are re-packed once per CTA into the canonical K-major operand layout and stay resident.
+//
+// Warp roles: 0 = bulk-copy producer, 1 = MMA issuer, 2 = TMEM allocator, 4-7 = epilogue (TMEM -> registers ->
+// bias/ReLU/LRN -> pooling by warp shuffles: the four pixels of a pooling window sit in lanes l, l^1, l^16, l^17).
+#include "../common/ptx.cuh"
+#include "../common/host_util.h"
+#include "../../include/dtm_b200.h"
+#include "plane_layout.cuh"
+
+namespace dtm {
+
+constexpr int C2_IN = 32;
+constexpr int C2_OUT = 64;
+constexpr int C2_K = 25 * C2_IN;                       // 800
+constexpr int C2_W_BYTES = C2_K * C2_OUT * 2;          // 102400
+constexpr int C2_IMG_BYTES = plane_image_bytes(C2_IN); // 16384
+constexpr int C2_BUFS = 2;
+constexpr int C2_SMEM = C2_W_BYTES + PL_GUARD_BYTES + C2_BUFS * C2_IMG_BYTES + PL_GUARD_BYTES + 128;
+
+constexpr float LRN2_BIAS = 1.0f;
+constexpr float LRN2_ALPHA = 0.001f / 9.0f;
+constexpr float LRN2_BETA = 0.75f;
+
+template <bool LRN>
+__global__ void __launch_bounds__(256, 1)
+conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ w2, const float* __restrict__ bias,
+                 int batch, __nv_bfloat16* __restrict__ p2, uint8_t* __restrict__ argmax, __nv_bfloat16* __restrict__ act2) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t img_full[C2_BUFS], img_empty[C2_BUFS], acc_full[2], acc_empty[2];
+  __shared__ uint32_t tmem_slot;
+  __shared__ float s_bias[C2_OUT];
+
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  uint8_t* s_w = smem;                                   // [k8 = 100][n = 64][8] bf16
+  uint8_t* s_guard = smem + C2_W_BYTES;                  // zero guard, image buffers, zero guard
+  uint8_t* s_img = s_guard + PL_GUARD_BYTES;
+
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t lane = lane_id();
+
+  // ---- one-time setup -------------------------------------------------------------------------
+  if (warp == 1 && elect_one()) {
+    for (int i = 0; i < C2_BUFS; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+    fence_mbar_init();
+  }
+  if (warp == 2) { tmem_alloc(&tmem_slot, 256); tmem_relinquish(); }
+  if (threadIdx.x < C2_OUT) s_bias[threadIdx.x] = bias[threadIdx.x];
+  {  // zero guards + image buffers (bottom halo of the last plane is the next buffer's first rows)
+    uint4 z = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x * 16; i < 2 * PL_GUARD_BYTES + C2_BUFS * C2_IMG_BYTES; i += blockDim.x * 16)
+      *reinterpret_cast<uint4*>(s_guard + i) = z;
+  }
+  // weights: TF layout [k = tap*32 + ci][n = co] (n contiguous) -> [k/8][n][k%8]
+  for (int chunk = threadIdx.x; chunk < (C2_K / 8) * C2_OUT; chunk += blockDim.x) {
+    const int k8 = chunk / C2_OUT, n = chunk % C2_OUT;
+    uint32_t v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint16_t lo = *reinterpret_cast<const uint16_t*>(w2 + (k8 * 8 + 2 * i) * C2_OUT + n);
+      const uint16_t hi = *reinterpret_cast<const uint16_t*>(w2 + (k8 * 8 + 2 * i + 1) * C2_OUT + n);
+      v[i] = static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+    }
+    *reinterpret_cast<uint4*>(s_w + chunk * 16) = make_uint4(v[0], v[1], v[2], v[3]);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  const int first = blockIdx.x;
+  const int stride = gridDim.x;
+
+  if (warp == 0) {
+    // ---- producer: one 16 KiB bulk copy per image ------------------------------------------------
+    if (elect_one()) {
+      int it = 0;
+      for (int img = first; img < batch; img += stride, ++it) {
+        const int b = it % C2_BUFS;
+        mbar_wait(&img_empty[b], ((it / C2_BUFS) & 1) ^ 1, 10);
+        mbar_arrive_expect_tx(&img_full[b], C2_IMG_BYTES);
+        bulk_load_1d(s_img + b * C2_IMG_BYTES, p1_planes + static_cast<size_t>(img) * C2_IMG_BYTES, C2_IMG_BYTES, &img_full[b]);
+      }
+    }
+  } else if (warp == 1) {
+    // ---- MMA issuer ----------------------------------------------------------------------------
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, C2_OUT, false, false);
+      const uint32_t w_base = smem_u32(s_w);
+      int it = 0;
+      for (int img = first; img < batch; img += stride, ++it) {
+        const int b = it % C2_BUFS;
+        const int a = it & 1;
+        mbar_wait(&acc_empty[a], ((it >> 1) & 1) ^ 1, 11);
+        mbar_wait(&img_full[b], (it / C2_BUFS) & 1, 12);
+        tc_fence_after();
+        const uint32_t img_base = smem_u32(s_img + b * C2_IMG_BYTES);
+#pragma unroll 1
+        for (int t = 0; t < 2; ++t) {
+          const uint32_t d_tmem = tmem_base + a * 128 + t * 64;
+#pragma unroll 1
+          for (int tap = 0; tap < 25; ++tap) {
+            const int kh = tap / 5, kw = tap % 5;
+            const uint32_t a_addr = img_base + (t * 128 + kh * PL_GRID + kw - 2) * 16;
+            const uint32_t b_addr = w_base + tap * 4 * (C2_OUT * 16);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const uint64_t da = umma_smem_desc(a_addr + j * 2 * PL_PLANE_BYTES, PL_PLANE_BYTES, 128, UMMA_SWIZZLE_NONE);
+              const uint64_t db = umma_smem_desc(b_addr + j * 2 * (C2_OUT * 16), C2_OUT * 16, 128, UMMA_SWIZZLE_NONE);
+              umma_f16(d_tmem, da, db, idesc, (tap | j) ? 1u : 0u);
+            }
+          }
+        }
+        umma_commit(&img_empty[b]);
+        umma_commit(&acc_full[a]);
+      }
+    }
+  } else if (warp >= 4) {
+    // ---- epilogue ------------------------------------------------------------------------------
+    const uint32_t q = warp & 3;
+    const int w_px = lane & 15;            // column inside the 16-wide grid
+    const int h_sub = lane >> 4;           // 0/1: row inside the warp's row pair
+    int it = 0;
+    for (int img = first; img < batch; img += stride, ++it) {
+      const int a = it & 1;
+      mbar_wait(&acc_full[a], (it >> 1) & 1, 13);
+      tc_fence_after();
+#pragma unroll 1
+      for (int t = 0; t < 2; ++t) {
+        const int h = t * 8 + q * 2 + h_sub;         // image row of this thread's pixel
+        const int ph = t * 4 + q, pw = w_px >> 1;    // pooled coordinates of its window
+        const bool writer = (lane < 16) && ((lane & 1) == 0) && pw < 7 && ph < 7;
+        const bool pixel_valid = h < IMG && w_px < IMG;
+        float v[C2_OUT];
+        {
+          uint32_t r[32];
+          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 128 + t * 64, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(__uint_as_float(r[j]) + s_bias[j], 0.0f);
+          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 128 + t * 64 + 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[32 + j] = fmaxf(__uint_as_float(r[j]) + s_bias[32 + j], 0.0f);
+        }
+        if (LRN) {
+          // act2 keeps the post-ReLU activation (bf16) for the backward pass; LRN runs on the rounded values
+#pragma unroll
+          for (int j = 0; j < C2_OUT; ++j) v[j] = __bfloat162float(__float2bfloat16(v[j]));
+          if (pixel_valid) {
+            uint4* dst = reinterpret_cast<uint4*>(act2 + (static_cast<size_t>(img) * (IMG * IMG) + h * IMG + w_px) * C2_OUT);
+#pragma unroll
+            for (int j = 0; j < C2_OUT; j += 8)
+              dst[j >> 3] = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
+                                       pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
+          }
+          float sq[C2_OUT];
+#pragma unroll
+          for (int j = 0; j < C2_OUT; ++j) sq[j] = v[j] * v[j];
+          float y[C2_OUT];
+#pragma unroll
+          for (int j = 0; j < C2_OUT; ++j) {
+            float s = 0.0f;
+#pragma unroll
+            for (int d = -4; d <= 4; ++d)
+              if (j + d >= 0 && j + d < C2_OUT) s += sq[j + d];
+            y[j] = v[j] * __powf(LRN2_BIAS + LRN2_ALPHA * s, -LRN2_BETA);
+          }
+#pragma unroll
+          for (int j = 0; j < C2_OUT; ++j) v[j] = y[j];
+        }
+        // 2x2 max-pool across lanes l, l^1 (w+1), l^16 (h+1), l^17
+        __nv_bfloat16* p2_dst = p2 + (static_cast<size_t>(img) * 49 + ph * 7 + pw) * C2_OUT;
+        uint8_t* am_dst = argmax + (static_cast<size_t>(img) * 49 + ph * 7 + pw) * C2_OUT;
+#pragma unroll
+        for (int j0 = 0; j0 < C2_OUT; j0 += 8) {
+          float best[8];
+          uint32_t arg_lo = 0, arg_hi = 0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float v00 = v[j0 + j];
+            const float v01 = __shfl_xor_sync(0xffffffffu, v00, 1);
+            const float v10 = __shfl_xor_sync(0xffffffffu, v00, 16);
+            const float v11 = __shfl_xor_sync(0xffffffffu, v00, 17);
+            float m = v00;
+            uint32_t arg = 0;
+            if (v01 > m) { m = v01; arg = 1; }
+            if (v10 > m) { m = v10; arg = 2; }
+            if (v11 > m) { m = v11; arg = 3; }
+            best[j] = m;
+            if (j < 4) arg_lo |= arg << (8 * j);
+            else       arg_hi |= arg << (8 * (j - 4));
+          }
+          if (writer) {
+            *reinterpret_cast<uint4*>(p2_dst + j0) = make_uint4(pack_bf16x2(best[0], best[1]), pack_bf16x2(best[2], best[3]),
+                                                                pack_bf16x2(best[4], best[5]), pack_bf16x2(best[6], best[7]));
+            *reinterpret_cast<uint2*>(am_dst + j0) = make_uint2(arg_lo, arg_hi);
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[a]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 256);
+}
+
+}  // namespace dtm
+
+extern "C" int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const float* bias, int batch, int lrn, void* p2,
+                             void* argmax, void* act2, void* stream) {
+  using namespace dtm;
+  if (batch <= 0) return dtm_fail("conv2_fwd: batch must be positive");
+  if (lrn && !act2) return dtm_fail("conv2_fwd: LRN needs the act2 buffer");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  static bool configured = false;
+  if (!configured) {
+    DTM_CUDA_OK(cudaFuncSetAttribute(conv2_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C2_SMEM));
+    DTM_CUDA_OK(cudaFuncSetAttribute(conv2_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C2_SMEM));
+    configured = true;
+  }
+  const int grid = min(batch, device_sm_count());
+  auto args = [&](auto kern) {
+    kern<<<grid, 256, C2_SMEM, s>>>(static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(w2_bf16), bias,
+                                    batch, static_cast<__nv_bfloat16*>(p2), static_cast<uint8_t*>(argmax),
+                                    static_cast<__nv_bfloat16*>(act2));
+  };
+  if (lrn) args(conv2_fwd_kernel<true>);
+  else     args(conv2_fwd_kernel<false>);
+  DTM_CUDA_OK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,141 @@
+// conv2 weight gradient on tcgen05 (autodiff of mnist_input.py:161):
+//   dW2[kh][kw][ci][co] = sum_{image, pixel} P1[pixel + tap][ci] * dZ2[pixel][co]
+//
+// Here the reduction (K) dimension is *pixels*.  Both operands are read straight from their plane-layout images
+// as MN-major UMMA operands: a plane's 8 pixels x 8 channels x 2 B block is a canonical MN-major core matrix
+// (channels contiguous, pixels 16 B apart), planes are the M/N groups (SBO = 4096 B), and the filter tap is once
+// more a re-based start address on the P1 side.  Per image and tap: 14 tcgen05.mma of shape 64(co) x 32(ci) x 16
+// (one per image row — the zero rows 0-1 of the dZ2 plane are skipped), accumulated over all images of the CTA
+// in TMEM.  25 taps x 32 columns exceed the 512 TMEM columns, so blockIdx.y splits the taps 13 / 12.
+// The M = 64 accumulator occupies TMEM lanes {0-15, 32-47, 64-79, 96-111} (measured: profiles/umma_probe_r1.json).
+#include "../common/ptx.cuh"
+#include "../common/host_util.h"
+#include "../../include/dtm_b200.h"
+#include "plane_layout.cuh"
+
+namespace dtm {
+
+constexpr int WG_CI = 32, WG_CO = 64;
+constexpr int WG_P1_BYTES = plane_image_bytes(WG_CI);    // 16384
+constexpr int WG_DZ_BYTES = plane_image_bytes(WG_CO);    // 32768
+constexpr int WG_STAGE_BYTES = PL_GUARD_BYTES + WG_P1_BYTES + PL_GUARD_BYTES + WG_DZ_BYTES;  // 53248
+constexpr int WG_STAGES = 3;
+constexpr int WG_SMEM = WG_STAGES * WG_STAGE_BYTES + 128;
+constexpr int WG_TAPS_Y0 = 13;
+
+__global__ void __launch_bounds__(256, 1)
+conv2_wgrad_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __restrict__ dz2_planes, int batch,
+                   float* __restrict__ dw2) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[WG_STAGES], empty_bar[WG_STAGES], done_bar;
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t lane = lane_id();
+  const int tap0 = blockIdx.y == 0 ? 0 : WG_TAPS_Y0;
+  const int ntaps = blockIdx.y == 0 ? WG_TAPS_Y0 : 25 - WG_TAPS_Y0;
+
+  if (warp == 1 && elect_one()) {
+    for (int i = 0; i < WG_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(&done_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) { tmem_alloc(&tmem_slot, 512); tmem_relinquish(); }
+  {  // zero the guards around every P1 buffer (taps over-read into them; they must hold finite zeros)
+    uint4 z = make_uint4(0, 0, 0, 0);
+    for (int s = 0; s < WG_STAGES; ++s) {
+      uint8_t* st = smem + s * WG_STAGE_BYTES;
+      for (int i = threadIdx.x * 16; i < PL_GUARD_BYTES; i += blockDim.x * 16) {
+        *reinterpret_cast<uint4*>(st + i) = z;
+        *reinterpret_cast<uint4*>(st + PL_GUARD_BYTES + WG_P1_BYTES + i) = z;
+      }
+    }
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int first = blockIdx.x, stride = gridDim.x;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int it = 0;
+      for (int img = first; img < batch; img += stride, ++it) {
+        const int s = it % WG_STAGES;
+        mbar_wait(&empty_bar[s], ((it / WG_STAGES) & 1) ^ 1, 30);
+        mbar_arrive_expect_tx(&full_bar[s], WG_P1_BYTES + WG_DZ_BYTES);
+        uint8_t* st = smem + s * WG_STAGE_BYTES;
+        bulk_load_1d(st + PL_GUARD_BYTES, p1_planes + static_cast<size_t>(img) * WG_P1_BYTES, WG_P1_BYTES, &full_bar[s]);
+        bulk_load_1d(st + 2 * PL_GUARD_BYTES + WG_P1_BYTES, dz2_planes + static_cast<size_t>(img) * WG_DZ_BYTES, WG_DZ_BYTES,
+                     &full_bar[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(64, WG_CI, true, true);
+      int it = 0;
+      for (int img = first; img < batch; img += stride, ++it) {
+        const int s = it % WG_STAGES;
+        mbar_wait(&full_bar[s], (it / WG_STAGES) & 1, 31);
+        tc_fence_after();
+        const uint32_t p1_base = smem_u32(smem + s * WG_STAGE_BYTES + PL_GUARD_BYTES);
+        const uint32_t dz_base = smem_u32(smem + s * WG_STAGE_BYTES + 2 * PL_GUARD_BYTES + WG_P1_BYTES);
+#pragma unroll 1
+        for (int ks = PL_ROW_OFF; ks < PL_GRID; ++ks) {   // one K step = one image row of 16 grid pixels
+          const uint64_t da = umma_smem_desc(dz_base + ks * 256, 128, PL_PLANE_BYTES, UMMA_SWIZZLE_NONE);
+          const uint32_t acc = (it > 0 || ks > PL_ROW_OFF) ? 1u : 0u;
+#pragma unroll 1
+          for (int tl = 0; tl < ntaps; ++tl) {
+            const int tap = tap0 + tl;
+            const int kh = tap / 5, kw = tap % 5;
+            const uint32_t b_addr = p1_base + ((ks + kh - 2) * PL_GRID + kw - 2) * 16;
+            const uint64_t db = umma_smem_desc(b_addr, 128, PL_PLANE_BYTES, UMMA_SWIZZLE_NONE);
+            umma_f16(tmem_base + tl * WG_CI, da, db, idesc, acc);
+          }
+        }
+        umma_commit(&empty_bar[s]);
+      }
+      umma_commit(&done_bar);
+    }
+  } else if (warp >= 4) {
+    const uint32_t q = warp & 3;
+    mbar_wait(&done_bar, 0, 32);
+    tc_fence_after();
+    const int co = q * 16 + lane;  // valid for lane < 16
+#pragma unroll 1
+    for (int tl = 0; tl < ntaps; ++tl) {
+      uint32_t r[32];
+      tmem_ld_x32(tmem_base + ((q * 32u) << 16) + tl * WG_CI, r);
+      tmem_ld_wait();
+      if (lane < 16) {
+        float* dst = dw2 + static_cast<size_t>(tap0 + tl) * WG_CI * WG_CO + co;
+#pragma unroll
+        for (int ci = 0; ci < WG_CI; ++ci) red_add_f32(dst + ci * WG_CO, __uint_as_float(r[ci]));
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace dtm
+
+extern "C" int dtm_conv2_wgrad(const void* p1_planes, const void* dz2_planes, int batch, float* dw2, void* stream) {
+  using namespace dtm;
+  if (batch <= 0) return dtm_fail("conv2_wgrad: batch must be positive");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  static bool configured = false;
+  if (!configured) {
+    DTM_CUDA_OK(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
+    configured = true;
+  }
+  const int gx = min(batch, max(1, device_sm_count() / 2));
+  conv2_wgrad_kernel<<<dim3(gx, 2), 256, WG_SMEM, s>>>(static_cast<const uint8_t*>(p1_planes),
+                                                      static_cast<const uint8_t*>(dz2_planes), batch, dw2);
+  DTM_CUDA_OK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,162 @@
+// The 10-class head of the MNIST CNN: softmax_linear (mnist_input.py:200-205), sparse softmax cross-entropy +
+// batch mean (:224-226), top-1 accuracy (:238-240), the NaN check that NanTensorHook performs on the host
+// (main.py:138) and the whole backward of the head, in two small CUDA-core kernels (N = 10 is GEMV-shaped; a
+// 128-row tensor-core tile would be 92 % padding).
+//
+//   head_forward : one warp per example.  logits = h . W + b ; loss/accuracy accumulated into the device-side
+//                  training state ; dlogits = (softmax - onehot) * grad_scale.
+//   head_backward: one CTA per 32 hidden units.  dH = dlogits . W^T, gated by the sign of the forward activation
+//                  (ReLU backward; for a dropped-out activation the stored h is 0, so the same test also applies
+//                  the dropout mask and only the 1/keep scale remains), dW = h^T . dlogits, both bias gradients.
+#include "../common/ptx.cuh"
+#include "../common/host_util.h"
+#include "../../include/dtm_b200.h"
+
+namespace dtm {
+
+constexpr int NCLS = 10;
+
+__global__ void __launch_bounds__(256)
+head_forward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, const float* __restrict__ w,
+                    const float* __restrict__ bias, const int* __restrict__ labels, float grad_scale, float loss_scale,
+                    float* __restrict__ logits_out, float* __restrict__ probs_out, float* __restrict__ dlogits,
+                    dtm_train_state* __restrict__ state) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const uint32_t lane = lane_id();
+  if (row >= batch) return;
+  float acc[NCLS];
+#pragma unroll
+  for (int c = 0; c < NCLS; ++c) acc[c] = 0.0f;
+  const __nv_bfloat16* hr = h + static_cast<size_t>(row) * hidden;
+  for (int k = lane; k < hidden; k += 32) {
+    const float hv = __bfloat162float(hr[k]);
+    const float2* wk = reinterpret_cast<const float2*>(w + static_cast<size_t>(k) * NCLS);  // 40-byte rows: 8-byte aligned
+#pragma unroll
+    for (int c2 = 0; c2 < NCLS / 2; ++c2) {
+      const float2 ww = wk[c2];
+      acc[2 * c2] = fmaf(hv, ww.x, acc[2 * c2]);
+      acc[2 * c2 + 1] = fmaf(hv, ww.y, acc[2 * c2 + 1]);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NCLS; ++c) acc[c] = warp_sum(acc[c]) + bias[c];
+  if (lane != 0) return;
+
+  float mx = acc[0];
+#pragma unroll
+  for (int c = 1; c < NCLS; ++c) mx = fmaxf(mx, acc[c]);
+  float e[NCLS], sum = 0.0f;
+#pragma unroll
+  for (int c = 0; c < NCLS; ++c) { e[c] = __expf(acc[c] - mx); sum += e[c]; }
+  const float inv = 1.0f / sum;
+  if (logits_out) {
+#pragma unroll
+    for (int c = 0; c < NCLS; ++c) logits_out[static_cast<size_t>(row) * NCLS + c] = acc[c];
+  }
+  if (probs_out) {
+#pragma unroll
+    for (int c = 0; c < NCLS; ++c) probs_out[static_cast<size_t>(row) * NCLS + c] = e[c] * inv;
+  }
+  if (!labels) return;
+  const int y = labels[row];
+  float target = 0.0f;
+  int greater = 0;
+#pragma unroll
+  for (int c = 0; c < NCLS; ++c) if (c == y) target = acc[c];
+#pragma unroll
+  for (int c = 0; c < NCLS; ++c) greater += (acc[c] > target) ? 1 : 0;
+  const float loss = (mx - target) + __logf(sum);
+  if (dlogits) {
+#pragma unroll
+    for (int c = 0; c < NCLS; ++c)
+      dlogits[static_cast<size_t>(row) * NCLS + c] = (e[c] * inv - (c == y ? 1.0f : 0.0f)) * grad_scale;
+  }
+  if (state) {
+    atomicAdd(&state->loss_sum, loss * loss_scale);
+    if (greater == 0) atomicAdd(&state->correct, loss_scale);
+    if (!(fabsf(loss) <= 3.0e38f)) atomicOr(&state->nan_flag, 1u);  // catches NaN and Inf
+  }
+}
+
+constexpr int HB_COLS = 32;
+
+__global__ void __launch_bounds__(256)
+head_backward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, const float* __restrict__ w,
+                     const float* __restrict__ dlogits, float inv_keep, __nv_bfloat16* __restrict__ dh,
+                     float* __restrict__ dw, float* __restrict__ db_out, float* __restrict__ db_hidden) {
+  __shared__ float s_red[8][NCLS + 1][HB_COLS + 1];
+  const int kk = threadIdx.x & 31;
+  const int r = threadIdx.x >> 5;
+  const int k = blockIdx.x * HB_COLS + kk;
+  const bool col_ok = k < hidden;
+  float wk[NCLS];
+#pragma unroll
+  for (int c = 0; c < NCLS; ++c) wk[c] = col_ok ? w[static_cast<size_t>(k) * NCLS + c] : 0.0f;
+  float adw[NCLS];
+#pragma unroll
+  for (int c = 0; c < NCLS; ++c) adw[c] = 0.0f;
+  float adb = 0.0f;
+  for (int b = blockIdx.y * 8 + r; b < batch; b += gridDim.y * 8) {
+    const float* dl = dlogits + static_cast<size_t>(b) * NCLS;   // same address across the warp: broadcast load
+    float d[NCLS];
+#pragma unroll
+    for (int c = 0; c < NCLS; ++c) d[c] = dl[c];
+    if (col_ok) {
+      const float hv = __bfloat162float(h[static_cast<size_t>(b) * hidden + k]);
+      float g = 0.0f;
+#pragma unroll
+      for (int c = 0; c < NCLS; ++c) { g = fmaf(d[c], wk[c], g); adw[c] = fmaf(hv, d[c], adw[c]); }
+      const __nv_bfloat16 gb = __float2bfloat16(hv > 0.0f ? g * inv_keep : 0.0f);
+      dh[static_cast<size_t>(b) * hidden + k] = gb;
+      adb += __bfloat162float(gb);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NCLS; ++c) s_red[r][c][kk] = adw[c];
+  s_red[r][NCLS][kk] = adb;
+  __syncthreads();
+  for (int i = threadIdx.x; i < (NCLS + 1) * HB_COLS; i += blockDim.x) {
+    const int c = i / HB_COLS, col = i % HB_COLS;
+    const int kq = blockIdx.x * HB_COLS + col;
+    if (kq >= hidden) continue;
+    float s = 0.0f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s += s_red[q][c][col];
+    if (c < NCLS) red_add_f32(dw + static_cast<size_t>(kq) * NCLS + c, s);
+    else if (db_hidden) red_add_f32(db_hidden + kq, s);
+  }
+  // output-bias gradient: column sums of dlogits, done once (first column block), split over blockIdx.y
+  if (blockIdx.x == 0 && threadIdx.x < NCLS) {
+    float s = 0.0f;
+    for (int b = blockIdx.y; b < batch; b += gridDim.y) s += dlogits[static_cast<size_t>(b) * NCLS + threadIdx.x];
+    red_add_f32(db_out + threadIdx.x, s);
+  }
+}
+
+}  // namespace dtm
+
+extern "C" int dtm_head_forward(const void* h, int batch, int hidden, const float* w, const float* bias, const int* labels,
+                                float grad_scale, float loss_scale, float* logits, float* probs, float* dlogits,
+                                dtm_train_state* state, void* stream) {
+  using namespace dtm;
+  if (batch <= 0 || hidden <= 0) return dtm_fail("head_forward: batch and hidden must be positive");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  head_forward_kernel<<<(batch + 7) / 8, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(h), batch, hidden, w, bias, labels,
+                                                     grad_scale, loss_scale, logits, probs, dlogits, state);
+  DTM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtm_head_backward(const void* h, int batch, int hidden, const float* w, const float* dlogits, float inv_keep,
+                                 void* dh, float* dw, float* db_out, float* db_hidden, void* stream) {
+  using namespace dtm;
+  if (batch <= 0 || hidden <= 0) return dtm_fail("head_backward: batch and hidden must be positive");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int col_blocks = (hidden + HB_COLS - 1) / HB_COLS;
+  int split = 1;
+  while (col_blocks * split < 2 * device_sm_count() && split * 16 <= batch && split < 16) split *= 2;
+  head_backward_kernel<<<dim3(col_blocks, split), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(h), batch, hidden, w, dlogits,
+                                                              inv_keep, static_cast<__nv_bfloat16*>(dh), dw, db_out, db_hidden);
+  DTM_CUDA_OK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,144 @@
+"""Python wrappers over the sm_100a kernels in libdtm_b200 (one function per C entry point).
+
+Tensors are torch CUDA tensors; every call is enqueued on the current torch CUDA stream, which makes the whole
+training step capturable into a CUDA graph.  Layout helpers for the "plane layout" live in :mod:`.layouts`.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_float, c_int, c_longlong, c_uint64, c_void_p
+
+import torch
+
+from . import _lib
+from ._lib import check, current_stream, ptr
+
+EPI_STORE_F32, EPI_BIAS_BF16, EPI_BIAS_RELU_BF16, EPI_MASK_BF16 = 0, 1, 2, 3
+OPT_SGD, OPT_MOMENTUM, OPT_ADAM = 0, 1, 2
+MAX_SEGMENTS = 16
+
+P, I, F = c_void_p, c_int, c_float
+_lib.register("dtm_conv1_fwd", [P, I, I, P, P, I, I, P, P, P, P])
+_lib.register("dtm_conv1_wgrad", [P, I, I, P, P, I, P, P, P])
+_lib.register("dtm_conv2_fwd", [P, P, P, I, I, P, P, P, P])
+_lib.register("dtm_conv2_dgrad", [P, P, P, P, I, I, P, P])
+_lib.register("dtm_conv2_wgrad", [P, P, I, P, P])
+_lib.register("dtm_unpool2", [P, P, P, I, I, P, P, P])
+_lib.register("dtm_colsum_bf16", [P, I, I, P, P])
+_lib.register("dtm_head_forward", [P, I, I, P, P, P, F, F, P, P, P, P, P])
+_lib.register("dtm_head_backward", [P, I, I, P, P, F, P, P, P, P, P])
+_lib.register("dtm_fused_update", [P, P, P, P, P, P, P, P, F, P])
+_lib.register("dtm_state_init", [P, c_longlong, F, F, P])
+
+
+class TrainState(ctypes.Structure):
+    """Mirror of ``dtm_train_state`` (include/dtm_b200.h)."""
+
+    _fields_ = [
+        ("global_step", ctypes.c_longlong),
+        ("beta1_power", c_float), ("beta2_power", c_float),
+        ("loss_sum", c_float), ("correct", c_float),
+        ("nan_flag", ctypes.c_uint), ("ticket", ctypes.c_uint),
+        ("last_xent", c_float), ("last_total", c_float), ("last_acc", c_float), ("last_lr", c_float),
+        ("wl_sum", c_float * MAX_SEGMENTS),
+        ("last_wl", c_float * MAX_SEGMENTS),
+        ("loss_avg", c_float * (MAX_SEGMENTS + 2)),
+    ]
+
+
+class UpdateConfig(ctypes.Structure):
+    """Mirror of ``dtm_update_config``."""
+
+    _fields_ = [
+        ("optimizer", c_int), ("n_segments", c_int), ("total", c_int), ("reserved", c_int),
+        ("decay_steps", ctypes.c_longlong),
+        ("base_lr", c_float), ("decay_rate", c_float), ("momentum", c_float), ("beta1", c_float), ("beta2", c_float),
+        ("epsilon", c_float), ("ema_decay", c_float),
+        ("seg_offset", c_int * (MAX_SEGMENTS + 1)),
+        ("seg_wd", c_float * MAX_SEGMENTS),
+        ("seg_zero_grad", c_int * MAX_SEGMENTS),
+    ]
+
+
+STATE_BYTES = ctypes.sizeof(TrainState)
+
+
+def _L():
+    return _lib.load()
+
+
+def gemm_bf16(a, a_mn_major, b, b_mn_major, d, M, N, K, *, epilogue=EPI_STORE_F32, bias=None, ref=None, alpha=1.0,
+              keep_prob=1.0, seed=0, step_ptr=None, split_k=1, ldd=None):
+    check(_L().dtm_gemm_bf16(ptr(a), int(a_mn_major), ptr(b), int(b_mn_major), ptr(d), M, N, K, ldd or N, epilogue,
+                             ptr(bias), ptr(ref), float(alpha), float(keep_prob), c_uint64(seed),
+                             c_void_p(step_ptr) if isinstance(step_ptr, int) else ptr(step_ptr), split_k,
+                             current_stream()), "gemm_bf16")
+
+
+def conv1_fwd(x, w, bias, p1_planes, argmax, pool_raw=None, *, channels=1, lrn=False):
+    batch = x.shape[0]
+    check(_L().dtm_conv1_fwd(ptr(x), int(x.dtype == torch.float32), channels, ptr(w), ptr(bias), batch, int(lrn),
+                             ptr(p1_planes), ptr(argmax), ptr(pool_raw), current_stream()), "conv1_fwd")
+
+
+def conv1_wgrad(x, grad_pooled, argmax, dw, db, *, channels=1):
+    batch = x.shape[0]
+    check(_L().dtm_conv1_wgrad(ptr(x), int(x.dtype == torch.float32), channels, ptr(grad_pooled), ptr(argmax), batch,
+                               ptr(dw), ptr(db), current_stream()), "conv1_wgrad")
+
+
+def conv2_fwd(p1_planes, w2_bf16, bias, p2, argmax, act2=None, *, batch, lrn=False):
+    check(_L().dtm_conv2_fwd(ptr(p1_planes), ptr(w2_bf16), ptr(bias), batch, int(lrn), ptr(p2), ptr(argmax), ptr(act2),
+                             current_stream()), "conv2_fwd")
+
+
+def conv2_dgrad(dz2_planes, w2_bf16, p1_planes, pool_raw, dpool1, *, batch, lrn=False):
+    check(_L().dtm_conv2_dgrad(ptr(dz2_planes), ptr(w2_bf16), ptr(p1_planes), ptr(pool_raw), batch, int(lrn), ptr(dpool1),
+                               current_stream()), "conv2_dgrad")
+
+
+def conv2_wgrad(p1_planes, dz2_planes, dw2, *, batch):
+    check(_L().dtm_conv2_wgrad(ptr(p1_planes), ptr(dz2_planes), batch, ptr(dw2), current_stream()), "conv2_wgrad")
+
+
+def unpool2(dp2, argmax, act2, dz2_planes, db2, *, batch, lrn=False):
+    check(_L().dtm_unpool2(ptr(dp2), ptr(argmax), ptr(act2), batch, int(lrn), ptr(dz2_planes), ptr(db2), current_stream()),
+          "unpool2")
+
+
+def colsum_bf16(x, out):
+    M, N = x.shape
+    check(_L().dtm_colsum_bf16(ptr(x), M, N, ptr(out), current_stream()), "colsum_bf16")
+
+
+def head_forward(h, w, bias, labels, *, grad_scale, loss_scale, logits=None, probs=None, dlogits=None, state=None):
+    batch, hidden = h.shape
+    check(_L().dtm_head_forward(ptr(h), batch, hidden, ptr(w), ptr(bias), ptr(labels), float(grad_scale), float(loss_scale),
+                                ptr(logits), ptr(probs), ptr(dlogits), ptr(state), current_stream()), "head_forward")
+
+
+def head_backward(h, w, dlogits, dh, dw, db_out, db_hidden, *, inv_keep=1.0):
+    batch, hidden = h.shape
+    check(_L().dtm_head_backward(ptr(h), batch, hidden, ptr(w), ptr(dlogits), float(inv_keep), ptr(dh), ptr(dw), ptr(db_out),
+                                 ptr(db_hidden), current_stream()), "head_backward")
+
+
+def fused_update(cfg: UpdateConfig, state, w, grad, slot0, slot1, ema, w_bf16, *, grad_scale=1.0):
+    check(_L().dtm_fused_update(ctypes.byref(cfg), ptr(state), ptr(w), ptr(grad), ptr(slot0), ptr(slot1), ptr(ema), ptr(w_bf16),
+                                float(grad_scale), current_stream()), "fused_update")
+
+
+def state_init(state, global_step=0, beta1=0.9, beta2=0.999):
+    check(_L().dtm_state_init(ptr(state), int(global_step), float(beta1), float(beta2), current_stream()), "state_init")
+
+
+def new_state(device) -> torch.Tensor:
+    """Allocate a device-resident ``dtm_train_state`` (as a uint8 tensor) and zero-initialise it."""
+    st = torch.zeros(STATE_BYTES, dtype=torch.uint8, device=device)
+    return st
+
+
+def read_state(state: torch.Tensor) -> TrainState:
+    """Synchronising device->host read of the training state."""
+    raw = bytes(state.cpu().numpy().tobytes())
+    return TrainState.from_buffer_copy(raw)

@@ -1,0 +1,266 @@
+"""The B200 execution engine: one training step = a fixed sequence of hand-written sm_100a kernels, replayed as a
+CUDA graph, with every piece of state (weights, optimizer slots, EMA shadows, global_step, loss averages) resident
+on the device.
+
+Replaces what the reference delegates to TensorFlow's executor inside ``mon_sess.run(train_op)`` (main.py:148-151):
+forward (mnist_input.py:118-208), loss/accuracy (:210-243), autodiff, optimizer apply + EMA + global_step (:246-270).
+Step schedule (``baseline`` preset; ``reference`` adds LRN inside the conv kernels and the local4 GEMMs):
+
+    conv1_fwd -> conv2_fwd[tcgen05] -> fc GEMM[tcgen05+TMA] -> head_forward(loss)         forward
+    head_backward -> dW3 GEMM || dP2 GEMM -> unpool2 -> conv2_wgrad || conv2_dgrad -> conv1_wgrad   backward
+    fused_update  (or, with >1 rank, the peer-memory all-reduce fused with the same update)       optimizer
+"""
+from __future__ import annotations
+
+import torch
+
+from ..models.params import FlatParams
+from ..models.presets import ModelSpec
+from ..ops import layouts, native
+
+
+class NativeEngine:
+    def __init__(self, spec: ModelSpec, batch_size: int, *, device="cuda", optimizer="adam", base_lr=1e-3, decay_rate=0.1,
+                 decay_steps=0, momentum=0.9, seed=0, comm=None, use_graph=True, keep_logits=False):
+        if batch_size % 8 != 0:
+            raise ValueError("the native engine needs a batch size that is a multiple of 8 (TMA row alignment)")
+        if not torch.cuda.is_available():
+            raise RuntimeError("NativeEngine requires a CUDA device (sm_100a); use TorchEngine on CPU")
+        from ..ops import _lib
+
+        _lib.load()  # fail loudly if the kernel library is missing
+        self.spec, self.B = spec, batch_size
+        self.device = torch.device(device)
+        self.comm = comm
+        self.world = comm.world_size if comm is not None else 1
+        self.seed = seed
+        self.use_graph = use_graph
+        self.optimizer = optimizer
+        alloc = comm.flat_allocator() if comm is not None else None
+        self.flat = FlatParams(spec, device=self.device, allocator=alloc)
+        self.cfg = self.flat.update_config(optimizer=optimizer, base_lr=base_lr, decay_rate=decay_rate,
+                                           decay_steps=decay_steps, momentum=momentum)
+        self.state = native.new_state(self.device)
+        native.state_init(self.state, 0, self.cfg.beta1, self.cfg.beta2)
+        self.eval_state = native.new_state(self.device)
+        native.state_init(self.eval_state)
+        self._alloc_activations(keep_logits)
+        self._graphs: dict[int, torch.cuda.CUDAGraph] = {}
+        self._side = torch.cuda.Stream(device=self.device)
+        self._fork_ev = [torch.cuda.Event() for _ in range(4)]
+        self.launches_per_step = 0
+
+    # ------------------------------------------------------------------------------------------------
+    def _alloc_activations(self, keep_logits: bool) -> None:
+        B, s, dev = self.B, self.spec, self.device
+        z = lambda *shape, dtype: torch.zeros(*shape, dtype=dtype, device=dev)
+        self.x = [z(B, s.image_pixels, dtype=torch.uint8) for _ in range(2)]
+        self.y = [z(B, dtype=torch.int32) for _ in range(2)]
+        self.xf = None  # float input staging for inference with pre-normalised images
+        self.p1 = layouts.alloc_planes(B, 32, dev)
+        self.arg1 = z(B, 196, 32, dtype=torch.uint8)
+        self.pool_raw = z(B, 196, 32, dtype=torch.bfloat16) if s.lrn else None
+        self.p2 = z(B, 3136, dtype=torch.bfloat16)
+        self.arg2 = z(B, 49, 64, dtype=torch.uint8)
+        self.act2 = z(B, 196, 64, dtype=torch.bfloat16) if s.lrn else None
+        self.h1 = z(B, s.fc1, dtype=torch.bfloat16)
+        self.h2 = z(B, s.fc2, dtype=torch.bfloat16) if s.fc2 else None
+        self.logits = z(B, 10, dtype=torch.float32)
+        self.probs = z(B, 10, dtype=torch.float32)
+        self.dlogits = z(B, 10, dtype=torch.float32)
+        self.dh_last = z(B, s.head_in, dtype=torch.bfloat16)
+        self.dh1 = z(B, s.fc1, dtype=torch.bfloat16) if s.fc2 else None
+        self.dp2 = z(B, 3136, dtype=torch.bfloat16)
+        self.dz2 = layouts.alloc_planes(B, 64, dev)
+        self.dpool1 = z(B, 196, 32, dtype=torch.bfloat16)
+
+    # ---- parameters / state ---------------------------------------------------------------------------
+    def load_params(self, tensors, *, ema=None, slots=None, global_step=0, loss_avg=None) -> None:
+        self.flat.load_dict({k: torch.as_tensor(v) for k, v in tensors.items()}, reset_ema=ema is None)
+        if ema:
+            self.flat.load_ema_dict(ema)
+        if slots:
+            for k, d in enumerate(slots):
+                if d:
+                    self.flat.load_slot_dict(k, d)
+        native.state_init(self.state, global_step, self.cfg.beta1, self.cfg.beta2)
+        if loss_avg:
+            st = native.read_state(self.state)
+            for i, v in enumerate(loss_avg):
+                st.loss_avg[i] = v
+            self.state.copy_(torch.frombuffer(bytearray(bytes(st)), dtype=torch.uint8).to(self.device))
+        torch.cuda.synchronize(self.device)
+
+    def params(self) -> dict[str, torch.Tensor]:
+        return {k: v.cpu() for k, v in self.flat.to_dict().items()}
+
+    def ema_params(self) -> dict[str, torch.Tensor]:
+        return {k: v.cpu() for k, v in self.flat.ema_dict().items()}
+
+    def slots(self) -> list[dict[str, torch.Tensor]]:
+        n = {"sgd": 0, "momentum": 1, "adam": 2}[self.optimizer.lower()]
+        return [{k: v.cpu() for k, v in self.flat.slot_dict(i).items()} for i in range(n)]
+
+    def gradients(self) -> dict[str, torch.Tensor]:
+        return {k: v.cpu() for k, v in self.flat.grad_dict().items()}
+
+    def read_state(self) -> native.TrainState:
+        return native.read_state(self.state)
+
+    @property
+    def state_ptr_step(self) -> int:
+        return self.state.data_ptr()  # global_step is the first field of dtm_train_state
+
+    # ---- the kernel sequence ----------------------------------------------------------------------------
+    def _forward(self, x, labels, *, training: bool, state, count=None) -> None:
+        s, f, B = self.spec, self.flat, self.B
+        n = 0
+        native.conv1_fwd(x, f.weight("conv1/weights"), f.weight("conv1/biases"), self.p1, self.arg1, self.pool_raw,
+                         channels=s.channels, lrn=s.lrn); n += 1
+        native.conv2_fwd(self.p1, f.weight_bf16("conv2/weights"), f.weight("conv2/biases"), self.p2, self.arg2, self.act2,
+                         batch=B, lrn=s.lrn); n += 1
+        drop_here = training and s.keep_prob < 1.0 and not s.fc2
+        native.gemm_bf16(self.p2, 0, f.weight_bf16("local3/weights"), 1, self.h1, B, s.fc1, 3136,
+                         epilogue=native.EPI_BIAS_RELU_BF16, bias=f.weight("local3/biases"),
+                         keep_prob=s.keep_prob if drop_here else 1.0, seed=self.seed, step_ptr=self.state_ptr_step); n += 1
+        h = self.h1
+        if s.fc2:
+            native.gemm_bf16(self.h1, 0, f.weight_bf16("local4/weights"), 1, self.h2, B, s.fc2, s.fc1,
+                             epilogue=native.EPI_BIAS_RELU_BF16, bias=f.weight("local4/biases")); n += 1
+            h = self.h2
+        native.head_forward(h, f.weight("softmax_linear/weights"), f.weight("softmax_linear/biases"), labels,
+                            grad_scale=1.0 / B, loss_scale=1.0 / B, logits=self.logits, probs=self.probs,
+                            dlogits=self.dlogits if training else None, state=state); n += 1
+        if count is not None:
+            count[0] += n
+
+    def _backward(self, x, count) -> None:
+        s, f, B = self.spec, self.flat, self.B
+        n = 0
+        h = self.h2 if s.fc2 else self.h1
+        inv_keep = 1.0 / s.keep_prob if (s.keep_prob < 1.0 and not s.fc2) else 1.0
+        native.head_backward(h, f.weight("softmax_linear/weights"), self.dlogits, self.dh_last,
+                             f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
+                             f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep); n += 1
+        if s.fc2:
+            # dW4 = h1^T . dY2 ; dY1 = (dY2 . W4^T) * [h1 > 0] ; db3 = colsum(dY1)
+            native.gemm_bf16(self.h1, 1, self.dh_last, 1, f.gradient("local4/weights"), s.fc1, s.fc2, B); n += 1
+            native.gemm_bf16(self.dh_last, 0, f.weight_bf16("local4/weights"), 0, self.dh1, B, s.fc1, s.fc2,
+                             epilogue=native.EPI_MASK_BF16, ref=self.h1); n += 1
+            native.colsum_bf16(self.dh1, f.gradient("local3/biases")); n += 1
+            dy1 = self.dh1
+        else:
+            dy1 = self.dh_last
+        main = torch.cuda.current_stream()
+        # fork: the two big fc GEMMs are independent
+        self._fork_ev[0].record(main)
+        self._side.wait_event(self._fork_ev[0])
+        with torch.cuda.stream(self._side):
+            native.gemm_bf16(self.p2, 1, dy1, 1, f.gradient("local3/weights"), 3136, s.fc1, B); n += 1
+            self._fork_ev[1].record(self._side)
+        native.gemm_bf16(dy1, 0, f.weight_bf16("local3/weights"), 0, self.dp2, B, 3136, s.fc1,
+                         epilogue=native.EPI_MASK_BF16, ref=self.p2); n += 1
+        native.unpool2(self.dp2, self.arg2, self.act2, self.dz2, f.gradient("conv2/biases"), batch=B, lrn=s.lrn); n += 1
+        # fork: conv2 wgrad runs beside dgrad -> conv1 wgrad
+        self._fork_ev[2].record(main)
+        self._side.wait_event(self._fork_ev[2])
+        with torch.cuda.stream(self._side):
+            native.conv2_wgrad(self.p1, self.dz2, f.gradient("conv2/weights"), batch=B); n += 1
+            self._fork_ev[3].record(self._side)
+        native.conv2_dgrad(self.dz2, f.weight_bf16("conv2/weights"), self.p1, self.pool_raw, self.dpool1, batch=B, lrn=s.lrn); n += 1
+        native.conv1_wgrad(x, self.dpool1, self.arg1, f.gradient("conv1/weights"), f.gradient("conv1/biases"),
+                           channels=s.channels); n += 1
+        main.wait_event(self._fork_ev[1])
+        main.wait_event(self._fork_ev[3])
+        count[0] += n
+
+    def _update(self, count) -> None:
+        f = self.flat
+        if self.comm is not None and self.world > 1:
+            self.comm.fused_allreduce_update(self.cfg, self.state, f)
+        else:
+            native.fused_update(self.cfg, self.state, f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, grad_scale=1.0)
+        count[0] += 1
+
+    def _step_body(self, slot: int) -> int:
+        count = [0]
+        self._forward(self.x[slot], self.y[slot], training=True, state=self.state, count=count)
+        self._backward(self.x[slot], count)
+        self._update(count)
+        return count[0]
+
+    # ---- public API -------------------------------------------------------------------------------------
+    def stage_batch(self, slot: int, images_u8: torch.Tensor, labels: torch.Tensor, stream=None) -> None:
+        """Asynchronous copy of a host (ideally pinned) or device batch into device slot ``slot``."""
+        with torch.cuda.stream(stream if stream is not None else torch.cuda.current_stream()):
+            self.x[slot].copy_(images_u8.view(self.B, -1), non_blocking=True)
+            self.y[slot].copy_(labels.view(self.B).to(torch.int32) if labels.dtype != torch.int32 else labels.view(self.B),
+                               non_blocking=True)
+
+    def train_step(self, slot: int = 0) -> None:
+        """Run one optimisation step on the batch staged in ``slot`` (asynchronous; no host sync)."""
+        if not self.use_graph:
+            self.launches_per_step = self._step_body(slot)
+            return
+        g = self._graphs.get(slot)
+        if g is None:
+            # warm-up outside capture (sets kernel attributes), then undo its effect on the state by re-capturing
+            snap = self._snapshot()
+            self.launches_per_step = self._step_body(slot)
+            torch.cuda.synchronize(self.device)
+            self._restore(snap)
+            g = torch.cuda.CUDAGraph()
+            cap = torch.cuda.Stream(device=self.device)
+            cap.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.graph(g, stream=cap):
+                self._step_body(slot)
+            torch.cuda.current_stream().wait_stream(cap)
+            self._restore(snap)
+            self._graphs[slot] = g
+        g.replay()
+
+    def _snapshot(self):
+        f = self.flat
+        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state]
+        return [b.clone() if b is not None else None for b in bufs]
+
+    def _restore(self, snap) -> None:
+        f = self.flat
+        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state]
+        for b, s in zip(bufs, snap):
+            if b is not None:
+                b.copy_(s)
+        torch.cuda.synchronize(self.device)
+
+    def forward_backward(self, slot: int = 0) -> None:
+        """Forward + backward only (gradients left in the flat buffer); used by tests and the summaries."""
+        count = [0]
+        self._forward(self.x[slot], self.y[slot], training=True, state=self.eval_state, count=count)
+        self._backward(self.x[slot], count)
+
+    def evaluate(self, slot: int = 0) -> tuple[float, float]:
+        """Loss and accuracy of the staged batch without touching weights (the reference's "test" summaries)."""
+        native.state_init(self.eval_state)
+        self._forward(self.x[slot], self.y[slot], training=False, state=self.eval_state)
+        st = native.read_state(self.eval_state)
+        return st.loss_sum, st.correct
+
+    def predict(self, images: torch.Tensor) -> torch.Tensor:
+        """Class probabilities for ``images`` ([n <= B, pixels], uint8 raw or float32 already normalised)."""
+        n = images.shape[0]
+        if n > self.B:
+            raise ValueError("predict: more images than the engine batch size")
+        if images.dtype == torch.uint8:
+            buf = self.x[0]
+        else:
+            if self.xf is None:
+                self.xf = torch.zeros(self.B, self.spec.image_pixels, dtype=torch.float32, device=self.device)
+            buf = self.xf
+        buf[:n].copy_(images.view(n, -1), non_blocking=True)
+        self._forward(buf, None, training=False, state=None)
+        return self.probs[:n].clone()
+
+    def metrics(self) -> dict:
+        st = self.read_state()
+        return {"global_step": st.global_step, "cross_entropy": st.last_xent, "total_loss": st.last_total,
+                "accuracy": st.last_acc, "lr": st.last_lr, "nan": bool(st.nan_flag)}

@@ -28,6 +28,43 @@ extern "C" {
 #define DTM_EPI_BIAS_RELU_BF16 2 /* D(bf16)  = dropout(relu(acc + bias))                              */
 #define DTM_EPI_MASK_BF16 3      /* D(bf16)  = acc * (ref > 0)      (ReLU backward)                   */
 
+/* Optimizers (reference: tf_parameter_mgr.getOptimizer(lr), mnist_input.py:261) */
+#define DTM_OPT_SGD 0
+#define DTM_OPT_MOMENTUM 1
+#define DTM_OPT_ADAM 2
+
+#define DTM_MAX_SEGMENTS 16
+
+/* Device-resident training state: everything the hot loop needs lives on the GPU so that a training step is a
+ * pure kernel sequence (CUDA-graph replayable, no host synchronisation).  Mirrors the scalar variables the
+ * reference keeps in its graph: global_step (main.py:83), beta powers of Adam, the loss moving averages
+ * (mnist_input.py:288-290), plus the loss/accuracy/NaN accumulators read by the hooks (main.py:104-107, :138). */
+typedef struct dtm_train_state {
+  long long global_step;
+  float beta1_power, beta2_power;
+  float loss_sum;          /* cross-entropy mean of the step in flight (accumulated by dtm_head_forward)   */
+  float correct;           /* accuracy of the step in flight                                              */
+  unsigned int nan_flag;   /* sticky: set when a non-finite loss is seen                                  */
+  unsigned int ticket;     /* internal: last-block election of the update kernels                         */
+  float last_xent, last_total, last_acc, last_lr; /* metrics of the last completed step                  */
+  float wl_sum[DTM_MAX_SEGMENTS];   /* sum of squares per variable (weights used by the step in flight)   */
+  float last_wl[DTM_MAX_SEGMENTS];  /* wd * l2_loss per variable of the last completed step               */
+  float loss_avg[DTM_MAX_SEGMENTS + 2]; /* EMA(0.9): per-variable weight_loss, [16] cross_entropy, [17] total_loss */
+} dtm_train_state;
+
+/* Flat parameter space: variables ("segments") are laid out back to back, each offset a multiple of 64 elements. */
+typedef struct dtm_update_config {
+  int optimizer;
+  int n_segments;
+  int total;                /* number of fp32 elements incl. padding (multiple of 64) */
+  int reserved;
+  long long decay_steps;
+  float base_lr, decay_rate, momentum, beta1, beta2, epsilon, ema_decay;
+  int seg_offset[DTM_MAX_SEGMENTS + 1];
+  float seg_wd[DTM_MAX_SEGMENTS];
+  int seg_zero_grad[DTM_MAX_SEGMENTS]; /* 1: gradient is accumulated with atomics and must be cleared after use */
+} dtm_update_config;
+
 /* ---- runtime ---------------------------------------------------------------------------------- */
 const char* dtm_last_error(void);
 int dtm_abi_version(void);
@@ -49,6 +86,51 @@ int dtm_umma_probe(const void* image, uint32_t image_bytes, const void* ops, uin
 int dtm_gemm_bf16(const void* a, int a_mn_major, const void* b, int b_mn_major, void* d, int M, int N, int K,
                   int ldd, int epilogue, const float* bias, const void* ref, float alpha, float keep_prob,
                   uint64_t seed, const long long* step_ptr, int split_k, void* stream);
+
+/* ---- conv1 (reference: mnist_input.py:39, :134-153) ----------------------------------------------------------- */
+/* x: uint8 [B][28*28*C] (in_is_float = 0, normalised x/255-0.5 in-kernel) or float32 already normalised.
+ * w: fp32 TF layout [5][5][C][32].  Outputs: p1_planes (plane layout, 32 ch), argmax uint8 [B][196][32],
+ * pool_raw bf16 [B][196][32] (only with lrn: the pooled activation before LRN, needed by the backward pass). */
+int dtm_conv1_fwd(const void* x, int in_is_float, int channels, const float* w, const float* bias, int batch, int lrn,
+                  void* p1_planes, void* argmax, void* pool_raw, void* stream);
+/* grad_pooled bf16 [B][196][32]: gradient w.r.t. the pooled activation, ReLU mask applied.  dw/db are accumulated
+ * (red.add) and must be zero on entry. */
+int dtm_conv1_wgrad(const void* x, int in_is_float, int channels, const void* grad_pooled, const void* argmax, int batch,
+                    float* dw, float* db, void* stream);
+
+/* ---- conv2 on tcgen05 (reference: mnist_input.py:156-172) ------------------------------------------------------ */
+/* w2_bf16: bf16 copy of the TF-layout weights [5][5][32][64].  p2: bf16 [B][7][7][64] (== [B][3136] in TF flatten
+ * order), argmax uint8 same shape, act2 bf16 [B][196][64] (only with lrn: post-ReLU, pre-LRN activation). */
+int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const float* bias, int batch, int lrn, void* p2,
+                  void* argmax, void* act2, void* stream);
+/* dz2_planes: plane layout, 64 ch (from dtm_unpool2).  dpool1: bf16 [B][196][32], gradient w.r.t. conv1's pooled
+ * activation with the ReLU mask (and LRN backward when lrn) applied. */
+int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, const void* p1_planes, const void* pool_raw, int batch,
+                    int lrn, void* dpool1, void* stream);
+/* dw2 fp32 [5][5][32][64], accumulated (red.add): zero on entry. */
+int dtm_conv2_wgrad(const void* p1_planes, const void* dz2_planes, int batch, float* dw2, void* stream);
+/* dp2 bf16 [B][49][64] -> dz2_planes (every byte of the valid region is written) ; db2[64] accumulated. */
+int dtm_unpool2(const void* dp2, const void* argmax, const void* act2, int batch, int lrn, void* dz2_planes, float* db2,
+                void* stream);
+int dtm_colsum_bf16(const void* x, int M, int N, float* out, void* stream);
+
+/* ---- classifier head + loss (reference: mnist_input.py:200-205, :224-226, :238-240; main.py:138) ---------------- */
+/* h bf16 [B][hidden]; w fp32 [hidden][10]; labels int32 (may be NULL for inference).  Any of logits / probs /
+ * dlogits ([B][10] fp32) / state may be NULL.  loss_scale is 1/B so that state->loss_sum is the batch mean. */
+int dtm_head_forward(const void* h, int batch, int hidden, const float* w, const float* bias, const int* labels,
+                     float grad_scale, float loss_scale, float* logits, float* probs, float* dlogits,
+                     dtm_train_state* state, void* stream);
+/* dh bf16 [B][hidden] = (dlogits . w^T) * [h > 0] * inv_keep ; dw [hidden][10], db_out [10], db_hidden [hidden]
+ * (may be NULL) are accumulated (red.add). */
+int dtm_head_backward(const void* h, int batch, int hidden, const float* w, const float* dlogits, float inv_keep, void* dh,
+                      float* dw, float* db_out, float* db_hidden, void* stream);
+
+/* ---- optimizer (reference: mnist_input.py:246-270) ------------------------------------------------------------ */
+/* One kernel: lr schedule, weight decay, SGD/Momentum/Adam, EMA(0.9999), bf16 shadow weights, loss averages,
+ * global_step++.  grad_scale multiplies the summed gradient (1/world_size).  slot0/slot1/ema/w_bf16 may be NULL. */
+int dtm_fused_update(const dtm_update_config* cfg, dtm_train_state* state, float* w, float* grad, float* slot0,
+                     float* slot1, float* ema, void* w_bf16, float grad_scale, void* stream);
+int dtm_state_init(dtm_train_state* state, long long global_step, float beta1, float beta2, void* stream);
 
 #ifdef __cplusplus
 }

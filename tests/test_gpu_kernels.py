@@ -1,0 +1,305 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 statement of the same op.
+
+Inputs are rounded to bf16 where the kernel consumes bf16, so the comparison isolates the kernel's own arithmetic
+(fp32 accumulation on tensor cores) from input quantisation.
+"""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _bf(x):
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+def _native():
+    from distributed_tensorflow_ibm_mnist_b200.ops import native, layouts, _lib
+
+    _lib.load()
+    return native, layouts
+
+
+def _rel_err(got, want):
+    return (got.float() - want.float()).abs().max().item() / (want.float().abs().max().item() + 1e-12)
+
+
+# ----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("a_mn,b_mn,M,N,K", [(0, 1, 512, 1024, 3136), (0, 0, 512, 3136, 1024), (1, 1, 3136, 1024, 512),
+                                            (0, 1, 200, 192, 1000), (1, 0, 256, 192, 1024)])
+def test_gemm_fp32_store(a_mn, b_mn, M, N, K):
+    native, _ = _native()
+    g = torch.Generator().manual_seed(M + N + K)
+    A = torch.randn(M, K, generator=g).to(torch.bfloat16)
+    B = torch.randn(K, N, generator=g).to(torch.bfloat16)
+    a = (A.t().contiguous() if a_mn else A).to(DEV)
+    b = (B if b_mn else B.t().contiguous()).to(DEV)
+    d = torch.empty(M, N, device=DEV, dtype=torch.float32)
+    native.gemm_bf16(a, a_mn, b, b_mn, d, M, N, K)
+    want = A.float() @ B.float()
+    assert _rel_err(d.cpu(), want) < 1e-4
+
+
+def test_gemm_split_k_accumulates():
+    native, _ = _native()
+    g = torch.Generator().manual_seed(3)
+    M, N, K = 256, 128, 2048
+    A = torch.randn(M, K, generator=g).to(torch.bfloat16)
+    B = torch.randn(K, N, generator=g).to(torch.bfloat16)
+    d = torch.zeros(M, N, device=DEV)
+    native.gemm_bf16(A.to(DEV), 0, B.to(DEV), 1, d, M, N, K, split_k=4, alpha=0.5)
+    assert _rel_err(d.cpu(), 0.5 * (A.float() @ B.float())) < 1e-4
+
+
+def test_gemm_bias_relu_dropout_and_mask():
+    native, _ = _native()
+    from distributed_tensorflow_ibm_mnist_b200.ops.philox import dropout_keep_mask
+
+    g = torch.Generator().manual_seed(5)
+    M, N, K = 384, 256, 512
+    A = torch.randn(M, K, generator=g).to(torch.bfloat16)
+    B = (torch.randn(K, N, generator=g) * 0.05).to(torch.bfloat16)
+    bias = torch.randn(N, generator=g)
+    step = torch.tensor([7], dtype=torch.int64, device=DEV)
+    d = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    native.gemm_bf16(A.to(DEV), 0, B.to(DEV), 1, d, M, N, K, epilogue=native.EPI_BIAS_RELU_BF16, bias=bias.to(DEV),
+                     keep_prob=0.5, seed=1234, step_ptr=step)
+    keep = torch.from_numpy(dropout_keep_mask(M, N, seed=1234, step=7, keep_prob=0.5))
+    want = torch.relu(A.float() @ B.float() + bias) * keep / 0.5
+    assert 0.4 < keep.float().mean().item() < 0.6
+    assert _rel_err(d.cpu(), want) < 1e-2
+    # ReLU-mask epilogue
+    ref = torch.randn(M, N, generator=g).to(torch.bfloat16)
+    d2 = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    native.gemm_bf16(A.to(DEV), 0, B.to(DEV), 1, d2, M, N, K, epilogue=native.EPI_MASK_BF16, ref=ref.to(DEV))
+    want2 = (A.float() @ B.float()) * (ref.float() > 0)
+    assert _rel_err(d2.cpu(), want2) < 1e-2
+
+
+# ----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("channels,lrn", [(1, False), (3, True)])
+def test_conv1_forward(channels, lrn):
+    native, layouts = _native()
+    from distributed_tensorflow_ibm_mnist_b200.models.oracle import tf_lrn
+
+    g = torch.Generator().manual_seed(11)
+    B = 37
+    x = torch.randint(0, 256, (B, 784 * channels), dtype=torch.uint8, generator=g)
+    w = torch.randn(5, 5, channels, 32, generator=g) * 0.2
+    b = torch.randn(32, generator=g) * 0.1
+    planes = layouts.alloc_planes(B, 32, DEV)
+    arg = torch.zeros(B, 196, 32, dtype=torch.uint8, device=DEV)
+    raw = torch.zeros(B, 196, 32, dtype=torch.bfloat16, device=DEV) if lrn else None
+    native.conv1_fwd(x.to(DEV), w.to(DEV), b.to(DEV), planes, arg, raw, channels=channels, lrn=lrn)
+    xin = (x.float() / 255 - 0.5).view(B, 28, 28, channels).permute(0, 3, 1, 2)
+    a1 = torch.relu(F.conv2d(xin, w.permute(3, 2, 0, 1), b, padding=2))
+    p1, idx = F.max_pool2d(a1, 2, return_indices=True)
+    want = p1
+    if lrn:
+        assert _rel_err(raw.float().cpu().view(B, 14, 14, 32), p1.permute(0, 2, 3, 1)) < 1e-2
+        want = tf_lrn(_bf(p1))
+    got = layouts.planes_to_nhwc(planes, 32).float().cpu()
+    assert _rel_err(got, want.permute(0, 2, 3, 1)) < 1e-2
+    assert layouts.planes_border_is_zero(planes, 32)
+    # arg-max: the position it names must hold the window maximum
+    a1w = a1.view(B, 32, 14, 2, 14, 2).permute(0, 2, 4, 1, 3, 5).reshape(B, 196, 32, 4)
+    picked = a1w.gather(3, arg.cpu().long().unsqueeze(-1)).squeeze(-1)
+    assert torch.allclose(picked, p1.permute(0, 2, 3, 1).reshape(B, 196, 32), atol=1e-4)
+
+
+@pytest.mark.parametrize("lrn", [False, True])
+def test_conv2_forward(lrn):
+    native, layouts = _native()
+    from distributed_tensorflow_ibm_mnist_b200.models.oracle import tf_lrn
+
+    g = torch.Generator().manual_seed(12)
+    B = 150  # > #SMs would be 148: exercises the persistent loop with uneven work
+    p1 = _bf(torch.relu(torch.randn(B, 14, 14, 32, generator=g)))
+    w2 = _bf(torch.randn(5, 5, 32, 64, generator=g) * 0.05)
+    b2 = torch.randn(64, generator=g) * 0.1
+    planes = layouts.nhwc_to_planes(p1.to(DEV))
+    p2 = torch.zeros(B, 49, 64, dtype=torch.bfloat16, device=DEV)
+    arg = torch.zeros(B, 49, 64, dtype=torch.uint8, device=DEV)
+    act2 = torch.zeros(B, 196, 64, dtype=torch.bfloat16, device=DEV) if lrn else None
+    native.conv2_fwd(planes, w2.to(torch.bfloat16).to(DEV), b2.to(DEV), p2, arg, act2, batch=B, lrn=lrn)
+    a2 = torch.relu(F.conv2d(p1.permute(0, 3, 1, 2), w2.permute(3, 2, 0, 1), b2, padding=2))
+    if lrn:
+        assert _rel_err(act2.float().cpu().view(B, 14, 14, 64), a2.permute(0, 2, 3, 1)) < 1e-2
+        a2 = tf_lrn(_bf(a2))
+    want = F.max_pool2d(a2, 2).permute(0, 2, 3, 1).reshape(B, 49, 64)
+    assert _rel_err(p2.cpu(), want) < 1e-2
+    a2w = a2.view(B, 64, 7, 2, 7, 2).permute(0, 2, 4, 1, 3, 5).reshape(B, 49, 64, 4)
+    picked = a2w.gather(3, arg.cpu().long().unsqueeze(-1)).squeeze(-1)
+    assert (picked - want).abs().max().item() <= 2e-2 * want.abs().max().item()
+
+
+def test_unpool2_and_conv2_backward():
+    native, layouts = _native()
+    g = torch.Generator().manual_seed(13)
+    B = 75
+    p1 = _bf(torch.relu(torch.randn(B, 14, 14, 32, generator=g)))
+    w2 = _bf(torch.randn(5, 5, 32, 64, generator=g) * 0.05)
+    dp2 = _bf(torch.randn(B, 49, 64, generator=g))
+    arg = torch.randint(0, 4, (B, 49, 64), dtype=torch.uint8, generator=g)
+    # route the pooled gradient back to 14x14 (oracle)
+    dz = torch.zeros(B, 7, 2, 7, 2, 64)
+    a = arg.view(B, 7, 7, 64).long()
+    for d in range(4):
+        dz[:, :, d >> 1, :, d & 1, :] = torch.where(a == d, dp2.view(B, 7, 7, 64), torch.zeros(()))
+    dz = dz.view(B, 14, 14, 64)
+    dz_planes = layouts.alloc_planes(B, 64, DEV)
+    db2 = torch.zeros(64, device=DEV)
+    native.unpool2(dp2.to(torch.bfloat16).to(DEV), arg.to(DEV), None, dz_planes, db2, batch=B)
+    assert torch.equal(layouts.planes_to_nhwc(dz_planes, 64).float().cpu(), dz)
+    assert layouts.planes_border_is_zero(dz_planes, 64)
+    assert _rel_err(db2.cpu(), dz.sum(dim=(0, 1, 2))) < 1e-4
+
+    # dgrad / wgrad oracles through autograd
+    p1v = p1.permute(0, 3, 1, 2).clone().requires_grad_(True)
+    wv = w2.permute(3, 2, 0, 1).clone().requires_grad_(True)
+    out = F.conv2d(p1v, wv, None, padding=2)
+    out.backward(dz.permute(0, 3, 1, 2))
+    want_dp1 = (p1v.grad * (p1v.detach() > 0)).permute(0, 2, 3, 1).reshape(B, 196, 32)
+    want_dw = wv.grad.permute(2, 3, 1, 0)
+
+    p1_planes = layouts.nhwc_to_planes(p1.to(DEV))
+    dpool1 = torch.zeros(B, 196, 32, dtype=torch.bfloat16, device=DEV)
+    native.conv2_dgrad(dz_planes, w2.to(torch.bfloat16).to(DEV), p1_planes, None, dpool1, batch=B)
+    assert _rel_err(dpool1.cpu(), want_dp1) < 1e-2
+
+    dw2 = torch.zeros(5, 5, 32, 64, device=DEV)
+    native.conv2_wgrad(p1_planes, dz_planes, dw2, batch=B)
+    assert _rel_err(dw2.cpu(), want_dw) < 1e-3
+
+
+def test_conv1_wgrad():
+    native, _ = _native()
+    g = torch.Generator().manual_seed(14)
+    B, C = 41, 1
+    x = torch.randint(0, 256, (B, 784 * C), dtype=torch.uint8, generator=g)
+    gp = _bf(torch.randn(B, 196, 32, generator=g) * (torch.rand(B, 196, 32, generator=g) > 0.5))
+    arg = torch.randint(0, 4, (B, 196, 32), dtype=torch.uint8, generator=g)
+    dz = torch.zeros(B, 14, 2, 14, 2, 32)
+    a = arg.view(B, 14, 14, 32).long()
+    for d in range(4):
+        dz[:, :, d >> 1, :, d & 1, :] = torch.where(a == d, gp.view(B, 14, 14, 32), torch.zeros(()))
+    dz = dz.view(B, 28, 28, 32).permute(0, 3, 1, 2)
+    xin = (x.float() / 255 - 0.5).view(B, 28, 28, C).permute(0, 3, 1, 2)
+    wv = torch.zeros(32, C, 5, 5, requires_grad=True)
+    F.conv2d(xin, wv, None, padding=2).backward(dz)
+    dw = torch.zeros(5, 5, C, 32, device=DEV)
+    db = torch.zeros(32, device=DEV)
+    native.conv1_wgrad(x.to(DEV), gp.to(torch.bfloat16).to(DEV), arg.to(DEV), dw, db, channels=C)
+    assert _rel_err(dw.cpu(), wv.grad.permute(2, 3, 1, 0)) < 1e-4
+    assert _rel_err(db.cpu(), dz.sum(dim=(0, 2, 3))) < 1e-4
+
+
+# ----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("hidden", [1024, 192])
+def test_head_forward_backward(hidden):
+    native, _ = _native()
+    g = torch.Generator().manual_seed(15)
+    B = 203
+    h = _bf(torch.relu(torch.randn(B, hidden, generator=g)))
+    w = torch.randn(hidden, 10, generator=g) * 0.05
+    b = torch.randn(10, generator=g) * 0.1
+    y = torch.randint(0, 10, (B,), dtype=torch.int32, generator=g)
+    state = native.new_state(DEV)
+    native.state_init(state)
+    logits = torch.empty(B, 10, device=DEV)
+    probs = torch.empty(B, 10, device=DEV)
+    dlog = torch.empty(B, 10, device=DEV)
+    native.head_forward(h.to(torch.bfloat16).to(DEV), w.to(DEV), b.to(DEV), y.to(DEV), grad_scale=1.0 / B, loss_scale=1.0 / B,
+                        logits=logits, probs=probs, dlogits=dlog, state=state)
+    hv = h.clone().requires_grad_(True)
+    wv = w.clone().requires_grad_(True)
+    bv = b.clone().requires_grad_(True)
+    lg = hv @ wv + bv
+    loss = F.cross_entropy(lg, y.long())
+    loss.backward()
+    st = native.read_state(state)
+    assert abs(st.loss_sum - loss.item()) < 1e-4 * max(1.0, abs(loss.item()))
+    target = lg.gather(1, y.long().view(-1, 1))
+    acc = ((lg > target).sum(1) == 0).float().mean().item()
+    assert abs(st.correct - acc) < 1e-5
+    assert st.nan_flag == 0
+    assert _rel_err(logits.cpu(), lg.detach()) < 1e-4
+    assert _rel_err(probs.cpu(), torch.softmax(lg.detach(), 1)) < 1e-4
+    dh = torch.empty(B, hidden, dtype=torch.bfloat16, device=DEV)
+    dw = torch.zeros(hidden, 10, device=DEV)
+    dbo = torch.zeros(10, device=DEV)
+    dbh = torch.zeros(hidden, device=DEV)
+    native.head_backward(h.to(torch.bfloat16).to(DEV), w.to(DEV), dlog, dh, dw, dbo, dbh, inv_keep=2.0)
+    want_dh = hv.grad * (h > 0) * 2.0
+    assert _rel_err(dh.cpu(), want_dh) < 1e-2
+    assert _rel_err(dw.cpu(), wv.grad) < 1e-4
+    assert _rel_err(dbo.cpu(), bv.grad) < 1e-4
+    assert _rel_err(dbh.cpu(), _bf(want_dh).sum(0)) < 1e-2
+
+
+def test_head_flags_nan():
+    native, _ = _native()
+    B, hidden = 16, 64
+    h = torch.full((B, hidden), float("nan"), dtype=torch.bfloat16, device=DEV)
+    w = torch.ones(hidden, 10, device=DEV)
+    b = torch.zeros(10, device=DEV)
+    y = torch.zeros(B, dtype=torch.int32, device=DEV)
+    state = native.new_state(DEV)
+    native.state_init(state)
+    native.head_forward(h, w, b, y, grad_scale=1.0, loss_scale=1.0, state=state)
+    assert native.read_state(state).nan_flag == 1
+
+
+def test_colsum():
+    native, _ = _native()
+    x = torch.randn(517, 200).to(torch.bfloat16)
+    out = torch.zeros(200, device=DEV)
+    native.colsum_bf16(x.to(DEV), out)
+    assert _rel_err(out.cpu(), x.float().sum(0)) < 1e-4
+
+
+# ----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind", ["sgd", "momentum", "adam"])
+def test_fused_update_matches_reference_optimizer(kind):
+    native, _ = _native()
+    from distributed_tensorflow_ibm_mnist_b200.models import oracle, presets
+    from distributed_tensorflow_ibm_mnist_b200.models.params import FlatParams
+
+    spec = presets.make_spec("reference")
+    params = oracle.init_params(spec, seed=3)
+    flat = FlatParams(spec, device=DEV)
+    flat.load_dict(params)
+    opt = oracle.ReferenceOptimizer({k: v.clone() for k, v in params.items()}, spec, optimizer=kind, base_lr=0.05,
+                                    decay_rate=0.5, decay_steps=2)
+    cfg = flat.update_config(optimizer=kind, base_lr=0.05, decay_rate=0.5, decay_steps=2)
+    state = native.new_state(DEV)
+    native.state_init(state)
+    g = torch.Generator().manual_seed(9)
+    for it in range(4):
+        grads = {k: torch.randn(v.shape, generator=g) * 0.01 for k, v in params.items()}
+        wl = oracle.weight_losses(opt.params, spec)
+        full = {k: grads[k] + (spec.var(k).wd or 0.0) * opt.params[k] for k in grads}
+        flat.load_grad_dict({k: 2.0 * v for k, v in grads.items()})   # "sum over 2 ranks"
+        native.fused_update(cfg, state, flat.w, flat.grad, flat.slot0, flat.slot1, flat.ema, flat.w_bf16, grad_scale=0.5)
+        lr = opt.step(full)
+        st = native.read_state(state)
+        assert st.global_step == it + 1
+        assert abs(st.last_lr - lr) < 1e-7
+        for v in spec.variables:
+            if v.wd:
+                assert abs(st.last_wl[flat.index[v.name]] - wl[v.name].item()) < 1e-3 * wl[v.name].item() + 1e-7
+    got = flat.to_dict()
+    tol = 3e-4 if kind == "adam" else 1e-5   # Adam divides by sqrt(v): fp32 rounding of tiny v is amplified
+    for k in params:
+        assert _rel_err(got[k].cpu(), opt.params[k]) < tol, k
+        assert _rel_err(flat.ema_dict()[k].cpu(), opt.ema[k]) < tol, k
+        assert _rel_err(flat.bf16_dict()[k].float().cpu(), opt.params[k]) < 1e-2, k
+    # atomically accumulated gradients are cleared, GEMM-stored ones are left alone
+    gd = flat.grad_dict()
+    assert gd["conv2/weights"].abs().sum().item() == 0.0
+    assert gd["local3/weights"].abs().sum().item() > 0.0
