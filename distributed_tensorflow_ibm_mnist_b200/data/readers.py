@@ -1,0 +1,182 @@
+"""Real-data input paths: TFRecord training stream with a shuffle buffer, 1-epoch readers for inference.
+
+* :class:`TFRecordBatches` — the training input of the reference: ``inputs(eval_data, batch_size)``
+  (mnist_input.py:44-73): file list -> existence check (ValueError) -> shuffled file order, infinite epochs ->
+  records parsed with the ``image_raw``/``label`` schema (:27-34) -> shuffle buffer with
+  ``min_after_dequeue = 1000`` and ``capacity = 1000 + 3 * batch`` (:67-71) filled by background threads.
+* :func:`iter_image_dir` / :func:`iter_tfrecord_examples` — the two single-epoch, unshuffled readers of
+  inference.py:38-65 (``*.jpg|jpeg|png`` decoded to one channel, label -1; or the validation TFRecords).
+"""
+from __future__ import annotations
+
+import glob
+import os
+import queue
+import random
+import threading
+
+import numpy as np
+import torch
+
+from ..formats.tfrecord import decode_example, read_records
+
+MIN_AFTER_DEQUEUE = 1000   # mnist_input.py:71
+
+
+def check_files(filenames: list[str]) -> None:
+    for f in filenames:
+        if not os.path.exists(f):
+            raise ValueError("Failed to find file: " + f)   # mnist_input.py:53-55
+
+
+def parse_record(record: bytes, image_bytes: int | None = None) -> tuple[np.ndarray, int]:
+    """``read_mnist``: uint8 pixels (still un-normalised) and int32 label — mnist_input.py:27-38."""
+    ex = decode_example(record)
+    raw = ex["image_raw"]
+    img = np.frombuffer(raw, dtype=np.uint8)
+    if image_bytes is not None and img.size != image_bytes:
+        raise ValueError(f"record holds {img.size} image bytes, expected {image_bytes} "
+                         "(28x28x3 = 2352 for reference-style RGB records, 784 for grey-scale)")
+    return img, int(ex["label"])
+
+
+class TFRecordBatches:
+    """Infinite stream of shuffled (uint8 [B, pixels], int32 [B]) batches read by background threads."""
+
+    def __init__(self, filenames: list[str], batch_size: int, image_bytes: int, *, num_threads: int = 2, seed: int = 0,
+                 shuffle: bool = True, min_after_dequeue: int = MIN_AFTER_DEQUEUE, pin: bool = False):
+        if not filenames:
+            raise ValueError("no input files")
+        check_files(filenames)
+        self.filenames, self.B, self.image_bytes = list(filenames), batch_size, image_bytes
+        self.capacity = min_after_dequeue + 3 * batch_size       # mnist_input.py:70
+        self.min_after = min_after_dequeue if shuffle else 0
+        self.shuffle = shuffle
+        self.pin = pin and torch.cuda.is_available()
+        self._rng = random.Random(seed)
+        self._q: queue.Queue = queue.Queue(maxsize=self.capacity)
+        self._buf: list[tuple[np.ndarray, int]] = []
+        self._stop = threading.Event()
+        self._err: list[BaseException] = []
+        self._threads = [threading.Thread(target=self._produce, args=(seed + 1 + i,), daemon=True) for i in range(num_threads)]
+        for t in self._threads:
+            t.start()
+
+    def _produce(self, seed: int) -> None:
+        rng = random.Random(seed)
+        try:
+            while not self._stop.is_set():
+                files = list(self.filenames)
+                if self.shuffle:
+                    rng.shuffle(files)
+                n = 0
+                for f in files:
+                    for rec in read_records(f):
+                        item = parse_record(rec, self.image_bytes)
+                        n += 1
+                        while not self._stop.is_set():
+                            try:
+                                self._q.put(item, timeout=0.1)
+                                break
+                            except queue.Full:
+                                continue
+                        if self._stop.is_set():
+                            return
+                if n == 0:
+                    raise ValueError("input files contain no records")
+        except BaseException as e:  # surfaced to the consumer
+            self._err.append(e)
+
+    def _get(self):
+        while True:
+            if self._err:
+                raise self._err[0]
+            try:
+                return self._q.get(timeout=0.2)
+            except queue.Empty:
+                continue
+
+    def next(self) -> tuple[torch.Tensor, torch.Tensor]:
+        # keep at least min_after_dequeue elements in the buffer while drawing uniformly from it (RandomShuffleQueue)
+        while len(self._buf) < self.min_after + self.B:
+            self._buf.append(self._get())
+        images = torch.empty(self.B, self.image_bytes, dtype=torch.uint8)
+        labels = torch.empty(self.B, dtype=torch.int32)
+        for i in range(self.B):
+            j = self._rng.randrange(len(self._buf)) if self.shuffle else 0
+            img, lab = self._buf[j]
+            if self.shuffle:
+                self._buf[j] = self._buf[-1]
+                self._buf.pop()
+            else:
+                self._buf.pop(0)
+            images[i] = torch.from_numpy(img.copy())
+            labels[i] = lab
+        if self.pin:
+            images, labels = images.pin_memory(), labels.pin_memory()
+        return images, labels
+
+    def close(self) -> None:
+        self._stop.set()
+
+    def __del__(self):
+        self._stop.set()
+
+
+# ---- single-epoch readers for inference ------------------------------------------------------------------
+IMAGE_EXTS = (".jpg", ".jpeg", ".png")
+
+
+def list_image_files(input_dir: str) -> list[str]:
+    """``glob(input_dir + '/*.*')`` filtered to .jpg/.jpeg/.png — inference.py:39-42 (sorted for determinism)."""
+    d = os.path.expanduser(input_dir)
+    return sorted(f for f in glob.iglob(os.path.join(d, "*.*")) if f.endswith(IMAGE_EXTS))
+
+
+def load_image_gray(path: str) -> np.ndarray:
+    """``tf.image.decode_image(value, channels=1)``: uint8 [H, W]."""
+    from PIL import Image
+
+    with Image.open(path) as im:
+        return np.asarray(im.convert("L"), dtype=np.uint8)
+
+
+def crop_or_pad(img: np.ndarray, size: int) -> np.ndarray:
+    """``tf.image.resize_image_with_crop_or_pad`` (centre crop / zero pad) to size x size — inference.py:73."""
+    h, w = img.shape[:2]
+    if h > size:
+        t = (h - size) // 2
+        img = img[t:t + size]
+    if w > size:
+        l = (w - size) // 2
+        img = img[:, l:l + size]
+    h, w = img.shape[:2]
+    if h < size or w < size:
+        out = np.zeros((size, size) + img.shape[2:], dtype=img.dtype)
+        t, l = (size - h) // 2, (size - w) // 2
+        out[t:t + h, l:l + w] = img
+        img = out
+    return img
+
+
+def per_image_standardization(img: np.ndarray) -> np.ndarray:
+    """``tf.image.per_image_standardization``: (x - mean) / max(stddev, 1/sqrt(N)) — inference.py:74."""
+    x = img.astype(np.float32)
+    n = x.size
+    std = max(float(x.std()), 1.0 / np.sqrt(n))
+    return (x - x.mean()) / std
+
+
+def iter_image_dir(input_dir: str):
+    """Yields (filename, uint8 [H, W] image, label=-1) — inference.py:38-47."""
+    for f in list_image_files(input_dir):
+        yield f, load_image_gray(f), -1
+
+
+def iter_tfrecord_examples(filenames: list[str]):
+    """Yields (key, uint8 flat image, label) over the files once, in order — inference.py:49-65."""
+    check_files(filenames)
+    for f in filenames:
+        for i, rec in enumerate(read_records(f)):
+            img, lab = parse_record(rec)
+            yield f"{f}:{i}", img, lab

@@ -89,3 +89,12 @@ class DeviceFeeder:
         self._used.add(slot)
         self._step += 1
         self._issue_copy(self._step % 2)   # prefetch the next batch while this step computes
+
+    def invalidate(self, slot: int) -> None:
+        """The slot was overwritten behind the feeder's back (e.g. by an evaluation batch): refill it."""
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.copy_stream.wait_event(ev)
+        images, labels = self.source.next()
+        self.engine.stage_batch(slot, images, labels, stream=self.copy_stream)
+        self.ready[slot].record(self.copy_stream)

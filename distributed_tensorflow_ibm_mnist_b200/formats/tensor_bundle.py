@@ -306,7 +306,7 @@ def _as_le_array(value) -> np.ndarray:
         arr = arr.astype(arr.dtype.newbyteorder("<"))
     if arr.dtype not in _NP_TO_DT:
         raise BundleError(f"dtype {arr.dtype} has no TensorFlow checkpoint representation here")
-    return np.ascontiguousarray(arr)
+    return np.ascontiguousarray(arr).reshape(arr.shape)   # ascontiguousarray promotes 0-d to 1-d
 
 
 def write_bundle(prefix: str, tensors: Mapping[str, np.ndarray], shard_of: Mapping[str, int] | None = None,

@@ -6,6 +6,7 @@ The reference reads such files with ``tf.TFRecordReader`` + ``parse_single_examp
 """
 from __future__ import annotations
 
+import os
 import struct
 from typing import BinaryIO, Iterable, Iterator
 
@@ -48,6 +49,7 @@ def frame(record: bytes) -> bytes:
 
 def read_records(path: str, verify: bool = True) -> Iterator[bytes]:
     """Iterate over the payloads of a TFRecord file; a truncated tail or CRC mismatch raises."""
+    size = os.path.getsize(path)
     with open(path, "rb") as f:
         while True:
             header = f.read(8)
@@ -61,6 +63,8 @@ def read_records(path: str, verify: bool = True) -> Iterator[bytes]:
             if verify and struct.unpack("<I", crc_len)[0] != masked_crc32c(header):
                 raise TFRecordCorruption(f"{path}: length crc mismatch")
             (length,) = struct.unpack("<Q", header)
+            if length > size - f.tell():
+                raise TFRecordCorruption(f"{path}: record length {length} exceeds the file size")
             data = f.read(length)
             crc_data = f.read(4)
             if len(data) < length or len(crc_data) < 4:

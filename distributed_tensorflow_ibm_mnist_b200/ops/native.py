@@ -29,6 +29,9 @@ _lib.register("dtm_head_forward", [P, I, I, P, P, P, F, F, P, P, P, P, P])
 _lib.register("dtm_head_backward", [P, I, I, P, P, F, P, P, P, P, P])
 _lib.register("dtm_fused_update", [P, P, P, P, P, P, P, P, F, P])
 _lib.register("dtm_state_init", [P, c_longlong, F, F, P])
+_lib.register("dtm_tensor_stats_scratch_bytes", [ctypes.c_size_t], ctypes.c_size_t)
+_lib.register("dtm_tensor_stats", [P, ctypes.c_size_t, I, P, P, ctypes.c_size_t, P])
+_lib.register("dtm_histogram", [P, ctypes.c_size_t, I, P, I, P, P])
 
 
 class TrainState(ctypes.Structure):
@@ -142,3 +145,22 @@ def read_state(state: torch.Tensor) -> TrainState:
     """Synchronising device->host read of the training state."""
     raw = bytes(state.cpu().numpy().tobytes())
     return TrainState.from_buffer_copy(raw)
+
+
+def tensor_stats_scratch_bytes(n: int) -> int:
+    return int(_L().dtm_tensor_stats_scratch_bytes(n))
+
+
+def tensor_stats(x: torch.Tensor, out6: torch.Tensor, scratch: torch.Tensor) -> None:
+    """min / max / sum / sumsq / count / L2-norm of a float32 or bfloat16 CUDA tensor into ``out6`` (6 floats)."""
+    if x.dtype not in (torch.float32, torch.bfloat16):
+        raise TypeError("tensor_stats: float32 or bfloat16 only")
+    x = x.contiguous()
+    check(_L().dtm_tensor_stats(ptr(x), x.numel(), int(x.dtype == torch.bfloat16), ptr(out6), ptr(scratch),
+                                scratch.numel() * scratch.element_size(), current_stream()), "tensor_stats")
+
+
+def histogram(x: torch.Tensor, limits: torch.Tensor, counts: torch.Tensor) -> None:
+    x = x.contiguous()
+    check(_L().dtm_histogram(ptr(x), x.numel(), int(x.dtype == torch.bfloat16), ptr(limits), limits.numel(), ptr(counts),
+                             current_stream()), "histogram")

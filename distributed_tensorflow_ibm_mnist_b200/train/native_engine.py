@@ -199,6 +199,7 @@ class NativeEngine:
 
     def train_step(self, slot: int = 0) -> None:
         """Run one optimisation step on the batch staged in ``slot`` (asynchronous; no host sync)."""
+        self._last_slot = slot
         if not self.use_graph:
             self.launches_per_step = self._step_body(slot)
             return
@@ -259,6 +260,31 @@ class NativeEngine:
         buf[:n].copy_(images.view(n, -1), non_blocking=True)
         self._forward(buf, None, training=False, state=None)
         return self.probs[:n].clone()
+
+    def activations(self) -> dict[str, torch.Tensor]:
+        """Layer outputs of the last forward pass (device tensors).  The conv layers are fused with their pooling
+        (and LRN) stage, so "conv1"/"conv2" are the pooled activations rather than the pre-pool ReLU outputs."""
+        out = {"conv1": layouts.planes_to_nhwc(self.p1, 32), "conv2": self.p2.view(self.B, 7, 7, 64), "local3": self.h1}
+        if self.h2 is not None:
+            out["local4"] = self.h2
+        out["softmax_linear"] = self.logits
+        return out
+
+    def summary_tensors(self) -> dict:
+        """Tensors for the chief's summaries (main.py:95-109).  Gradients are recomputed on the last batch with an extra
+        forward/backward pass: the fused update kernel clears accumulated gradients as it consumes them."""
+        slot = getattr(self, "_last_slot", 0)
+        self.flat.grad.zero_()
+        self.forward_backward(slot)
+        grads = {v.name: self.flat.gradient(v.name).clone() for v in self.spec.variables}
+        self.flat.grad.zero_()
+        params = {v.name: self.flat.weight(v.name) for v in self.spec.variables}
+        return {"params": params, "activations": self.activations(), "gradients": grads}
+
+    def scalar_state(self) -> dict:
+        st = self.read_state()
+        return {"global_step": int(st.global_step), "beta1_power": float(st.beta1_power), "beta2_power": float(st.beta2_power),
+                "loss_avg": [float(v) for v in st.loss_avg]}
 
     def metrics(self) -> dict:
         st = self.read_state()

@@ -132,6 +132,17 @@ int dtm_fused_update(const dtm_update_config* cfg, dtm_train_state* state, float
                      float* slot1, float* ema, void* w_bf16, float grad_scale, void* stream);
 int dtm_state_init(dtm_train_state* state, long long global_step, float beta1, float beta2, void* stream);
 
+/* ---- summary statistics (reference: main.py:95-109 through monitor_cb) ----------------------------------------- */
+/* out6 = {min, max, sum, sum of squares, element count, L2 norm}.  `scratch` is device memory of at least
+ * dtm_tensor_stats_scratch_bytes(n) bytes, 8-byte aligned, whose first 64 bytes are zero before the first call
+ * (the kernel leaves them zero again); calls sharing one scratch buffer must not overlap on the GPU. */
+size_t dtm_tensor_stats_scratch_bytes(size_t n);
+int dtm_tensor_stats(const void* x, size_t n, int is_bf16, float* out6, void* scratch, size_t scratch_bytes, void* stream);
+/* counts[nbins] (float, accumulated) over the sorted bucket limits (device doubles), TensorFlow histogram rule. */
+int dtm_histogram(const void* x, size_t n, int is_bf16, const double* limits, int nbins, float* counts, void* stream);
+/* host helper: CRC-32C of a host buffer, continuing from `crc` (TFRecord / checkpoint / event-file codecs). */
+uint32_t dtm_crc32c(const char* data, size_t n, uint32_t crc);
+
 #ifdef __cplusplus
 }
 #endif

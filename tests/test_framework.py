@@ -1,0 +1,392 @@
+"""CPU tests of the framework layer: flags, parameter manager, cluster roles, model semantics (closed-form checks from
+SURVEY §2f), optimizer / EMA formulas, checkpoint save-resume, data readers, dataset conversion, monitor."""
+import json
+import math
+import os
+import struct
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from distributed_tensorflow_ibm_mnist_b200.cluster import spec as cluster_spec
+from distributed_tensorflow_ibm_mnist_b200.config import flags as flags_mod
+from distributed_tensorflow_ibm_mnist_b200.config import parameter_mgr as pm
+from distributed_tensorflow_ibm_mnist_b200.models import oracle, presets
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+# ---- flags ------------------------------------------------------------------------------------------------
+def _fresh_flags():
+    fv = flags_mod._FlagValues()
+    fv._define("job_name", "", "", str)
+    fv._define("task_id", 0, "", int)
+    fv._define("lr", 0.5, "", float)
+    fv._define("log_device_placement", False, "", flags_mod._to_bool)
+    fv.alias("task_index", "task_id")
+    return fv
+
+
+def test_flags_tf_style_syntax():
+    fv = _fresh_flags()
+    rest = fv.parse(["--job_name=worker", "--task_index", "3", "-lr=0.25", "--log_device_placement", "positional"])
+    assert (fv.job_name, fv.task_id, fv.task_index, fv.lr, fv.log_device_placement) == ("worker", 3, 3, 0.25, True)
+    assert rest == ["positional"]
+    fv.parse(["--nolog_device_placement"])
+    assert fv.log_device_placement is False
+    fv.parse(["--log_device_placement=true", "--task_id=7"])
+    assert fv.log_device_placement is True and fv.task_id == 7
+    with pytest.raises(flags_mod.FlagError):
+        fv.parse(["--unknown=1"])
+    with pytest.raises(flags_mod.FlagError):
+        fv.parse(["--task_id=abc"])
+    assert fv.parse(["--unknown=1"], known_only=True) == ["--unknown=1"]
+    fv.task_id = 0      # the reference assigns FLAGS.task_id = 0 in local mode (main.py:66)
+    assert fv.task_id == 0
+
+
+# ---- parameter manager -------------------------------------------------------------------------------------
+def test_parameter_manager_getters_and_file(tmp_path):
+    pm.reset()
+    assert pm.getTrainBatchSize() == 128 and pm.getMaxSteps() == 1000
+    f = tmp_path / "hp.json"
+    f.write_text(json.dumps({"max_steps": 42, "test_interval": 7, "train_batch_size": 64, "base_learning_rate": 0.05,
+                             "learning_rate_decay": 0.5, "optimizer": "momentum", "train_data": "a.tfr,b.tfr"}))
+    pm.load_file(str(f))
+    assert (pm.getMaxSteps(), pm.getTestInterval(), pm.getTrainBatchSize()) == (42, 7, 64)
+    assert (pm.getBaseLearningRate(), pm.getLearningRateDecay()) == (0.05, 0.5)
+    assert pm.getTrainData() == ["a.tfr", "b.tfr"] and pm.getTestData() == [] and pm.getValData() == []
+    opt = pm.getOptimizer(0.05)
+    assert opt.kind == "momentum" and opt.slot_names() == ["Momentum"]
+    with pytest.raises(KeyError):
+        pm.configure(not_a_param=1)
+    pm.configure(optimizer="rmsprop")
+    with pytest.raises(ValueError):
+        pm.getOptimizer(0.1)
+    pm.reset()
+
+
+# ---- cluster ---------------------------------------------------------------------------------------------
+def test_cluster_roles_follow_reference_rules():
+    c = cluster_spec.ClusterSpec.from_flags("h:1", "h:2,h:3")
+    assert c.as_dict() == {"worker": ["h:2", "h:3"], "ps": ["h:1"]} and not c.is_local
+    assert c.rendezvous() == ("h", 1)
+    r = cluster_spec.resolve_role(c, "worker", 1)
+    assert (r.rank, r.world_size, r.is_chief) == (1, 2, False)
+    assert cluster_spec.resolve_role(c, "worker", 0).is_chief
+    assert cluster_spec.resolve_role(c, "ps", 0).rank == -1
+    with pytest.raises(ValueError):
+        cluster_spec.resolve_role(c, "worker", 2)
+    with pytest.raises(ValueError):
+        cluster_spec.resolve_role(c, "", 0)
+    # ps hosts alone do not make a cluster: local mode, task 0, chief (main.py:56, :63-66)
+    loc = cluster_spec.ClusterSpec.from_flags("h:1", "")
+    assert loc.is_local
+    r = cluster_spec.resolve_role(loc, "worker", 5)
+    assert (r.task_id, r.is_chief, r.world_size) == (0, True, 1)
+    assert cluster_spec.ClusterSpec.from_flags("", "h:9").rendezvous() == ("h", 9)
+
+
+# ---- model semantics -----------------------------------------------------------------------------------------
+def test_parameter_counts_and_schedule_constants():
+    assert presets.make_spec("reference").num_params == 3_464_714
+    assert presets.make_spec("reference", channels=1).num_params == 3_463_114
+    assert presets.make_spec("baseline").num_params == 3_274_634
+    assert presets.make_spec("wide").num_params == 25_832_330
+    assert presets.decay_steps(128) == 136_718
+    names = [v.name for v in presets.make_spec("reference").variables]
+    assert names == ["conv1/weights", "conv1/biases", "conv2/weights", "conv2/biases", "local3/weights", "local3/biases",
+                     "local4/weights", "local4/biases", "softmax_linear/weights", "softmax_linear/biases"]
+    assert presets.make_spec("reference").var("conv1/weights").shape == (5, 5, 3, 32)
+
+
+def test_initialisers_match_reference():
+    spec = presets.make_spec("reference")
+    p = oracle.init_params(spec, seed=1)
+    assert torch.all(p["conv1/biases"] == 0) and torch.all(p["conv2/biases"] == 0.1) and torch.all(p["local3/biases"] == 0.1)
+    w = p["local3/weights"]
+    assert w.abs().max() <= 2 * 0.04 + 1e-7 and abs(w.std().item() - 0.04 * 0.8796) < 2e-3   # truncated at 2 sigma
+    assert p["softmax_linear/weights"].abs().max() <= 2 / 192 + 1e-9
+
+
+def test_tf_lrn_semantics():
+    x = torch.randn(2, 12, 3, 3)
+    got = oracle.tf_lrn(x)
+    want = torch.empty_like(x)
+    for c in range(12):
+        lo, hi = max(0, c - 4), min(12, c + 5)
+        s = (x[:, lo:hi] ** 2).sum(1)
+        want[:, c] = x[:, c] / (1.0 + (0.001 / 9.0) * s) ** 0.75
+    assert torch.allclose(got, want, atol=1e-6)
+
+
+def test_loss_is_xent_plus_weight_decay_and_accuracy_rule():
+    spec = presets.make_spec("reference")
+    p = oracle.init_params(spec, seed=0)
+    x = torch.rand(8, spec.image_pixels) - 0.5
+    y = torch.randint(0, 10, (8,))
+    logits = oracle.forward(p, x, spec)
+    assert logits.shape == (8, 10)
+    total, xent = oracle.loss_fn(logits, y, p, spec)
+    wd = 0.004 * 0.5 * (p["local3/weights"] ** 2).sum() + 0.004 * 0.5 * (p["local4/weights"] ** 2).sum()
+    assert abs(float(total) - float(xent + wd)) < 1e-5
+    assert abs(float(xent) - float(F.cross_entropy(logits, y))) < 1e-6
+    lg = torch.tensor([[1.0, 1.0, 0.0], [0.0, 2.0, 1.0]])
+    assert float(oracle.accuracy_fn(lg, torch.tensor([0, 2]))) == 0.5   # tie counts as correct, lower score does not
+
+
+def test_forward_shapes_all_presets():
+    for name in ("reference", "baseline", "wide"):
+        spec = presets.make_spec(name)
+        p = oracle.init_params(spec, seed=0)
+        logits, acts = oracle.forward(p, torch.zeros(2, spec.image_pixels), spec, return_activations=True)
+        assert logits.shape == (2, 10) and acts["conv1"].shape == (2, 32, 28, 28) and acts["conv2"].shape == (2, 64, 14, 14)
+
+
+def test_learning_rate_and_ema_formulas():
+    assert oracle.learning_rate(0.1, 0.5, 10, 9) == 0.1
+    assert oracle.learning_rate(0.1, 0.5, 10, 10) == 0.05
+    assert oracle.learning_rate(0.1, 0.5, 10, 25) == 0.025
+    assert oracle.ema_keep(0) == 0.1 and abs(oracle.ema_keep(90) - 0.91) < 1e-12 and oracle.ema_keep(10 ** 7) == 0.9999
+
+
+@pytest.mark.parametrize("kind", ["sgd", "momentum", "adam"])
+def test_reference_optimizer_matches_hand_computation(kind):
+    spec = presets.make_spec("baseline")
+    w0 = torch.tensor([1.0, -2.0])
+    g = torch.tensor([0.5, 0.25])
+    params = {"w": w0.clone()}
+    opt = oracle.ReferenceOptimizer(params, spec, optimizer=kind, base_lr=0.1, decay_rate=0.5, decay_steps=1, momentum=0.9)
+    opt.step({"w": g})
+    opt.step({"w": g})
+    if kind == "sgd":
+        want = w0 - 0.1 * g - 0.05 * g
+    elif kind == "momentum":
+        a1 = g
+        a2 = 0.9 * a1 + g
+        want = w0 - 0.1 * a1 - 0.05 * a2
+    else:
+        m1, v1 = 0.1 * g, 0.001 * g * g
+        s1 = w0 - 0.1 * math.sqrt(1 - 0.999) / (1 - 0.9) * m1 / (v1.sqrt() + 1e-8)
+        m2, v2 = 0.9 * m1 + 0.1 * g, 0.999 * v1 + 0.001 * g * g
+        want = s1 - 0.05 * math.sqrt(1 - 0.999 ** 2) / (1 - 0.9 ** 2) * m2 / (v2.sqrt() + 1e-8)
+    assert torch.allclose(params["w"], want, atol=1e-6)
+    assert opt.global_step == 2
+    # EMA with num_updates: d0 = 0.1, d1 = 2/11
+    e1 = w0 - 0.9 * (w0 - (want if False else None)) if False else None  # noqa: F841 (formula spelled out below)
+    first = {"sgd": w0 - 0.1 * g, "momentum": w0 - 0.1 * g}.get(kind)
+    if first is not None:
+        ema1 = w0 - (1 - 0.1) * (w0 - first)
+        ema2 = ema1 - (1 - 2 / 11) * (ema1 - want)
+        assert torch.allclose(opt.ema["w"], ema2, atol=1e-6)
+
+
+# ---- engine + checkpoint ---------------------------------------------------------------------------------------
+def _torch_engine(preset="reference", B=8, **kw):
+    from distributed_tensorflow_ibm_mnist_b200.train.torch_engine import TorchEngine
+
+    spec = presets.make_spec(preset)
+    eng = TorchEngine(spec, B, optimizer=kw.pop("optimizer", "adam"), base_lr=kw.pop("base_lr", 1e-3), **kw)
+    eng.load_params(oracle.init_params(spec, seed=0))
+    return spec, eng
+
+
+def test_torch_engine_learns_separable_data():
+    from distributed_tensorflow_ibm_mnist_b200.data.synthetic import SyntheticMnist
+
+    spec, eng = _torch_engine("baseline", B=32, optimizer="momentum", base_lr=0.05)
+    src = SyntheticMnist(32, spec.image_pixels, pool_batches=4, seed=0, separable=True, pin=False)
+    first = last = None
+    for i in range(30):
+        eng.stage_batch(0, *src.next())
+        eng.train_step(0)
+        m = eng.metrics()
+        first = first if first is not None else m["cross_entropy"]
+        last = m["cross_entropy"]
+    assert last < 0.5 * first and m["global_step"] == 30 and not m["nan"]
+    probs = eng.predict(src.images[0])
+    assert probs.shape == (32, 10) and torch.allclose(probs.sum(1), torch.ones(32), atol=1e-5)
+
+
+def test_checkpoint_inventory_resume_and_rotation(tmp_path):
+    from distributed_tensorflow_ibm_mnist_b200.formats import checkpoint_state as cs
+    from distributed_tensorflow_ibm_mnist_b200.formats.tensor_bundle import BundleReader
+    from distributed_tensorflow_ibm_mnist_b200.train import checkpointing as ck
+
+    spec, eng = _torch_engine("reference", B=4)
+    x = torch.randint(0, 256, (4, spec.image_pixels), dtype=torch.uint8)
+    y = torch.randint(0, 10, (4,), dtype=torch.int32)
+    d = str(tmp_path / "train")
+    prefixes = []
+    for i in range(7):
+        eng.stage_batch(0, x, y)
+        eng.train_step(0)
+        prefixes.append(ck.save_checkpoint(d, eng, spec, "adam", num_shards=2, max_to_keep=5))
+    rd = BundleReader(prefixes[-1])
+    keys = set(rd.keys())
+    expect = {"global_step", "beta1_power", "beta2_power", "cross_entropy/avg", "total_loss/avg"}
+    for v in spec.variables:
+        expect |= {v.name, v.name + "/ExponentialMovingAverage", v.name + "/Adam", v.name + "/Adam_1"}
+    expect |= {f"{l}/weight_loss/avg" for l in ("conv1", "conv2", "local3", "local4", "softmax_linear")}
+    assert keys == expect
+    assert rd.num_shards == 2 and int(rd.get("global_step")) == 7 and rd.entry("global_step").dtype == 9
+    assert rd.entry("conv1/weights/Adam").shard_id == rd.entry("conv1/weights").shard_id      # slots co-located
+    st = cs.read_state(d)
+    assert st.model_checkpoint_path == "model.ckpt-7" and st.all_model_checkpoint_paths == [f"model.ckpt-{i}" for i in range(3, 8)]
+    assert not os.path.exists(prefixes[0] + ".index") and os.path.exists(prefixes[-1] + ".index")
+    # resume into a fresh engine: bit-exact variables, optimizer state and step
+    spec2, eng2 = _torch_engine("reference", B=4)
+    assert ck.restore_checkpoint(d, eng2, spec2, "adam") == 7
+    for k, v in eng.params().items():
+        assert torch.equal(v, eng2.params()[k])
+    for a, b in zip(eng.slots(), eng2.slots()):
+        for k in a:
+            assert torch.equal(a[k], b[k])
+    for k, v in eng.ema_params().items():
+        assert torch.equal(v, eng2.ema_params()[k])
+    assert eng2.metrics()["global_step"] == 7
+    eng.stage_batch(0, x, y); eng.train_step(0)
+    eng2.stage_batch(0, x, y); eng2.train_step(0)
+    for k, v in eng.params().items():
+        assert torch.allclose(v, eng2.params()[k], atol=1e-7), k
+    assert ck.restore_checkpoint(str(tmp_path / "nothing"), eng2, spec2, "adam") is None
+
+
+def test_checkpoint_channel_adaptation_for_inference(tmp_path):
+    from distributed_tensorflow_ibm_mnist_b200.train import checkpointing as ck
+
+    spec3, eng3 = _torch_engine("reference", B=4)           # 3-channel training graph
+    d = str(tmp_path)
+    ck.save_checkpoint(d, eng3, spec3, "adam")
+    spec1 = presets.make_spec("reference", channels=1)
+    from distributed_tensorflow_ibm_mnist_b200.train.torch_engine import TorchEngine
+
+    eng1 = TorchEngine(spec1, 4)
+    ck.restore_checkpoint(d, eng1, spec1, "sgd", model_only=True)
+    grey = torch.randint(0, 256, (4, 784), dtype=torch.uint8)
+    rgb = grey.view(4, 784, 1).repeat(1, 1, 3).view(4, 2352)
+    assert torch.allclose(eng1.predict(grey), eng3.predict(rgb), atol=1e-5)
+
+
+# ---- data ------------------------------------------------------------------------------------------------
+def _write_idx(tmp, n=30):
+    rng = np.random.default_rng(0)
+    imgs = rng.integers(0, 256, (n, 28, 28), dtype=np.uint8)
+    labs = rng.integers(0, 10, n).astype(np.uint8)
+    for split, (fi, fl) in {"training": ("train-images.idx3-ubyte", "train-labels.idx1-ubyte"),
+                            "testing": ("t10k-images.idx3-ubyte", "t10k-labels.idx1-ubyte")}.items():
+        with open(os.path.join(tmp, fi), "wb") as f:
+            f.write(struct.pack(">IIII", 2051, n, 28, 28) + imgs.tobytes())
+        with open(os.path.join(tmp, fl), "wb") as f:
+            f.write(struct.pack(">II", 2049, n) + labs.tobytes())
+    return imgs, labs
+
+
+def test_convert_mnist_idx_to_png_to_tfrecord_roundtrip(tmp_path):
+    sys.path.insert(0, ROOT)
+    import convert_mnist
+    from distributed_tensorflow_ibm_mnist_b200.data import readers
+    from distributed_tensorflow_ibm_mnist_b200.formats import tfrecord
+
+    src = tmp_path / "idx"; src.mkdir()
+    imgs, labs = _write_idx(str(src))
+    lbl, data, size, rows, cols = convert_mnist.read("training", str(src))
+    assert (size, rows, cols) == (30, 28, 28) and list(lbl) == list(labs)
+    with pytest.raises(ValueError):
+        convert_mnist.read("validation", str(src))
+    out = tmp_path / "png"
+    assert convert_mnist.main(["convert_mnist.py", str(src), str(out), "--quiet"]) == 0
+    f0 = out / "training" / str(labs[0]) / "0.png"
+    assert f0.exists() and np.array_equal(readers.load_image_gray(str(f0)), imgs[0])
+    rec = tmp_path / "train.tfrecord"
+    assert convert_mnist.main(["convert_mnist.py", "png2tfrecord", str(out / "training"), str(rec), "--channels=3"]) == 0
+    exs = [tfrecord.decode_example(r) for r in tfrecord.read_records(str(rec))]
+    assert len(exs) == 30 and all(len(e["image_raw"]) == 2352 for e in exs)
+    by_label = sorted(labs.tolist())
+    assert [e["label"] for e in exs] == by_label
+    first = np.frombuffer(exs[0]["image_raw"], np.uint8).reshape(28, 28, 3)
+    assert np.array_equal(first[..., 0], first[..., 2])
+    assert convert_mnist.main(["convert_mnist.py"]) == 2
+
+
+def test_tfrecord_batches_shuffle_and_validation(tmp_path):
+    from distributed_tensorflow_ibm_mnist_b200.data import readers
+    from distributed_tensorflow_ibm_mnist_b200.formats import tfrecord
+
+    p = str(tmp_path / "d.tfrecord")
+    n = 300
+    imgs = [bytes([i % 256]) * 784 for i in range(n)]
+    tfrecord.write_mnist_tfrecord(p, imgs, [i % 10 for i in range(n)])
+    with pytest.raises(ValueError, match="Failed to find file"):
+        readers.TFRecordBatches([p, str(tmp_path / "missing")], 8, 784)
+    ds = readers.TFRecordBatches([p], 16, 784, min_after_dequeue=50, seed=1)
+    assert ds.capacity == 50 + 3 * 16
+    x, y = ds.next()
+    assert x.shape == (16, 784) and x.dtype == torch.uint8 and y.dtype == torch.int32
+    assert all(int(x[i, 0]) % 10 == int(y[i]) for i in range(16))           # image/label pairs stay together
+    seen = [int(v) for _ in range(10) for v in ds.next()[0][:, 0]]
+    assert seen != sorted(seen)                                              # shuffled
+    ds.close()
+    bad = readers.TFRecordBatches([p], 4, 2352, min_after_dequeue=0)
+    with pytest.raises(ValueError, match="expected 2352"):
+        bad.next()
+    bad.close()
+    got = list(readers.iter_tfrecord_examples([p]))
+    assert len(got) == n and got[3][2] == 3 and got[0][0].endswith(":0")
+
+
+def test_image_preprocessing_helpers():
+    from distributed_tensorflow_ibm_mnist_b200.data import readers
+
+    img = np.arange(30 * 20, dtype=np.uint8).reshape(30, 20)
+    out = readers.crop_or_pad(img, 28)
+    assert out.shape == (28, 28) and np.array_equal(out[:, 4:24], img[1:29]) and out[:, :4].sum() == 0
+    s = readers.per_image_standardization(np.random.default_rng(0).integers(0, 255, (28, 28)).astype(np.uint8))
+    assert abs(s.mean()) < 1e-5 and abs(s.std() - 1) < 1e-4
+    flat = readers.per_image_standardization(np.full((28, 28), 7, np.uint8))
+    assert np.all(flat == 0)                                                  # stddev floor 1/sqrt(N)
+
+
+def test_monitor_collects_reference_summaries():
+    from distributed_tensorflow_ibm_mnist_b200.formats import proto
+    from distributed_tensorflow_ibm_mnist_b200.train import monitor as mc
+
+    mon = mc.CMonitor("/tmp/x", 10, 100)
+    for layer in ["conv1", "local3"]:
+        mon.SummaryHist("weight", layer + "/weights:0", layer)
+        mon.SummaryHist("activation", layer + "/" + layer + ":0", layer)
+        mon.SummaryNorm2("weight", layer + "/weights:0", layer)
+    mon.SummaryGradient("weight", "loss")
+    mon.SummaryGWRatio()
+    mon.SummaryScalar("train loss", "loss"); mon.SummaryScalar("test accuracy", "accuracy")
+    t = {"params": {"conv1/weights": torch.ones(5, 5, 1, 32), "local3/weights": torch.full((4, 4), 2.0)},
+         "activations": {"conv1": torch.zeros(2, 3), "local3": torch.ones(2, 3)},
+         "gradients": {"conv1/weights": torch.full((5, 5, 1, 32), 0.5), "local3/weights": torch.ones(4, 4)}}
+    tags = {}
+    for f, _, v in proto.parse(mon.collect(mc.DLMAO_TRAIN_SUMMARIES, t, {"loss": 1.5, "accuracy": 0.25})):
+        d = proto.parse_dict(v)
+        tags[d[1][0].decode()] = d
+    assert {"train loss", "conv1/weight", "conv1/activation", "conv1/weight_norm2", "local3/weight_norm2",
+            "conv1/weight_gradient", "conv1/gradient_weight_ratio", "local3/gradient_weight_ratio"} <= set(tags)
+    norm = struct.unpack("<f", struct.pack("<I", tags["local3/weight_norm2"][2][0]))[0]
+    ratio = struct.unpack("<f", struct.pack("<I", tags["conv1/gradient_weight_ratio"][2][0]))[0]
+    assert abs(norm - 8.0) < 1e-5 and abs(ratio - 0.5) < 1e-5
+    test_tags = [proto.parse_dict(v)[1][0].decode() for f, _, v in proto.parse(mon.collect(mc.DLMAO_TEST_SUMMARIES, t, {"loss": 1.0, "accuracy": 0.5}))]
+    assert test_tags == ["test accuracy"]
+
+
+def test_inference_helper_result_files(tmp_path):
+    from distributed_tensorflow_ibm_mnist_b200.utils import inference_helper as ih
+
+    probs = np.array([[0.7, 0.2, 0.1] + [0] * 7, [0.05, 0.9, 0.05] + [0] * 7], np.float32)
+    lab = tmp_path / "labels.txt"
+    lab.write_text("\n".join(f"digit{i}" for i in range(10)))
+    doc = ih.writeClassificationResult(str(tmp_path / "o" / "r.json"), ["a.png", "b.png"], probs, prob_thresh=0.15, label_file=str(lab))
+    assert [p["label"] for p in doc["results"][0]["predictions"]] == ["digit0", "digit1"]
+    assert json.load(open(tmp_path / "o" / "r.json"))["num_samples"] == 2
+    doc = ih.writeClassificationResult(str(tmp_path / "v.json"), ["k0", "k1"], probs, ground_truth=[0, 3])
+    assert doc["accuracy"] == 0.5 and doc["results"][1]["correct"] is False

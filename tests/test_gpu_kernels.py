@@ -303,3 +303,32 @@ def test_fused_update_matches_reference_optimizer(kind):
     gd = flat.grad_dict()
     assert gd["conv2/weights"].abs().sum().item() == 0.0
     assert gd["local3/weights"].abs().sum().item() > 0.0
+
+
+# ----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,dtype", [(10, torch.float32), (3211264, torch.float32), (100352 * 64, torch.bfloat16)])
+def test_tensor_stats_and_histogram(n, dtype):
+    native, _ = _native()
+    from distributed_tensorflow_ibm_mnist_b200.formats import events
+
+    g = torch.Generator().manual_seed(n)
+    x = (torch.randn(n, generator=g) * 0.05).to(dtype)
+    xd = x.to(DEV)
+    out = torch.zeros(6, device=DEV)
+    scratch = torch.zeros(native.tensor_stats_scratch_bytes(n), dtype=torch.uint8, device=DEV)
+    for _ in range(2):  # second call re-uses the scratch: the ticket must have been reset
+        native.tensor_stats(xd, out, scratch)
+    xf = x.double()
+    want = torch.tensor([xf.min(), xf.max(), xf.sum(), (xf * xf).sum(), float(n), (xf * xf).sum().sqrt()])
+    got = out.cpu().double()
+    assert torch.allclose(got[:2], want[:2], rtol=0, atol=0)
+    assert abs(got[2] - want[2]) <= 1e-5 * xf.abs().sum()
+    assert torch.allclose(got[3:], want[3:], rtol=1e-5)
+    limits = torch.from_numpy(events._BUCKET_LIMITS).to(DEV)
+    counts = torch.zeros(limits.numel(), device=DEV)
+    native.histogram(xd, limits, counts)
+    import numpy as np
+
+    idx = np.minimum(np.searchsorted(events._BUCKET_LIMITS, x.double().numpy(), side="right"), len(events._BUCKET_LIMITS) - 1)
+    ref = np.bincount(idx, minlength=len(events._BUCKET_LIMITS))
+    assert np.array_equal(counts.cpu().numpy().astype(np.int64), ref)
