@@ -1,0 +1,386 @@
+// Peer-memory communication over NVLink 5 / NVSwitch — the replacement for the reference's gRPC parameter-server
+// traffic (variable pulls main.py:80-93, gradient pushes + Apply ops mnist_input.py:262-264, global_step sync,
+// SURVEY §2f X1-X5).  No NCCL on this path: kernels load and store peer GPUs' memory directly.
+//
+//   symmetric memory   every rank cudaMalloc's the same buffers and exchanges CUDA IPC handles once; a kernel gets
+//                      the N peer base pointers by value (dtm_peer_ctx).
+//   cross-GPU barrier  flags[N] per rank in symmetric memory; rank r publishes a monotonically increasing epoch into
+//                      slot r of every peer (st.release.sys) and waits for all its own slots (ld.acquire.sys).
+//                      Inside a kernel CTA 0 does the NVLink part, the other CTAs wait on a local flag; kernels are
+//                      launched cooperatively so that all CTAs are co-resident.  Every spin has a watchdog.
+//   fused step         [barrier] -> reduce-scatter (each rank sums its 1/N shard of the flat gradient from all peers,
+//                      16-byte P2P loads, fixed rank order => bit-identical everywhere) -> 1/N scale + weight decay +
+//                      SGD/Momentum/Adam + EMA on the shard *in registers* (optimizer state is sharded) ->
+//                      all-gather of the updated fp32 weights by P2P stores into every peer -> [barrier] ->
+//                      local pass: bf16 shadow weights, clear accumulated gradients, step bookkeeping.
+//                      Link bytes per GPU and direction: (N-1)/N * S in (gradients) and out (weights).
+//   all-reduce         stand-alone fp32 sum on a symmetric buffer: one-shot (every rank reads everything; latency
+//                      optimal for small messages) or two-shot (reduce-scatter + all-gather; bandwidth optimal).
+//   broadcast          every rank pulls the root's buffer (initial parameters, restored checkpoints, global_step).
+#include "../common/ptx.cuh"
+#include "../common/host_util.h"
+#include "../optim/update_math.cuh"
+#include "../../include/dtm_b200.h"
+
+namespace dtm {
+
+struct CommCtrl {          // rank-local control block (device memory, zero-initialised once)
+  unsigned int epoch;      // last barrier epoch used
+  unsigned int arrive;     // intra-kernel CTA arrival counter
+  unsigned int go;         // intra-kernel release flag (epoch value)
+  unsigned int ticket;     // last-CTA election
+};
+
+DTM_DEVICE unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+DTM_DEVICE void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+DTM_DEVICE unsigned int ld_acquire_gpu(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+DTM_DEVICE void st_release_gpu(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+DTM_DEVICE void red_release_gpu_add(unsigned int* p, unsigned int v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// peer loads/stores: system scope so that they are never served from a stale L1 line
+DTM_DEVICE float4 ld_peer_v4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+DTM_DEVICE void st_peer_v4(float* p, float4 v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// Ranks may reach a collective seconds apart (start-up, graph capture), so cross-GPU waits get a longer leash than
+// the intra-kernel pipelines: ~2 minutes of SM clocks.
+constexpr long long COMM_WATCHDOG_CYCLES = 240000000000ll;
+
+DTM_DEVICE void spin_until_ge_sys(const unsigned int* p, unsigned int target, int tag) {
+  const long long t0 = clock64();
+  while (static_cast<int>(ld_acquire_sys(p) - target) < 0)
+    if (clock64() - t0 > COMM_WATCHDOG_CYCLES) watchdog_trap("peer barrier (a rank did not arrive)", tag, (int)target);
+}
+DTM_DEVICE void spin_until_ge_gpu(const unsigned int* p, unsigned int target, int tag) {
+  const long long t0 = clock64();
+  while (static_cast<int>(ld_acquire_gpu(p) - target) < 0)
+    if (clock64() - t0 > COMM_WATCHDOG_CYCLES) watchdog_trap("grid barrier", tag, (int)target);
+}
+
+// All CTAs of the kernel on all ranks rendezvous; `k` is the epoch value to publish (strictly increasing).
+DTM_DEVICE void cross_gpu_barrier(const dtm_peer_ctx& ctx, CommCtrl* ctrl, unsigned int k) {
+  __syncthreads();
+  if (blockIdx.x == 0) {
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      if (gridDim.x > 1) {
+        const long long t0 = clock64();
+        while (ld_acquire_gpu(&ctrl->arrive) != gridDim.x - 1)
+          if (clock64() - t0 > COMM_WATCHDOG_CYCLES) watchdog_trap("grid arrive", (int)k, 0);
+        ctrl->arrive = 0;
+        __threadfence();
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < ctx.world) {
+      st_release_sys(ctx.flags[threadIdx.x] + ctx.rank, k);
+      spin_until_ge_sys(ctx.flags[ctx.rank] + threadIdx.x, k, threadIdx.x);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_gpu(&ctrl->go, k);
+  } else if (threadIdx.x == 0) {
+    __threadfence_system();
+    red_release_gpu_add(&ctrl->arrive, 1u);
+    spin_until_ge_gpu(&ctrl->go, k, 1);
+  }
+  __syncthreads();
+}
+
+// Sum of one float4 over all ranks, fixed rank order (bit-identical whichever rank computes it).  The compile-time
+// rank count lets every peer load be issued before the first add: N-1 NVLink round trips overlap instead of chaining.
+template <int NR>
+DTM_DEVICE float4 reduce_peers_fixed(float* const* bufs, int i) {
+  float4 v[NR];
+#pragma unroll
+  for (int j = 0; j < NR; ++j) v[j] = ld_peer_v4(bufs[j] + i);
+  float4 a = v[0];
+#pragma unroll
+  for (int j = 1; j < NR; ++j) { a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w; }
+  return a;
+}
+DTM_DEVICE float4 reduce_peers(float* const* bufs, int world, int i) {
+  switch (world) {
+    case 2: return reduce_peers_fixed<2>(bufs, i);
+    case 4: return reduce_peers_fixed<4>(bufs, i);
+    case 8: return reduce_peers_fixed<8>(bufs, i);
+    default: break;
+  }
+  float4 a = ld_peer_v4(bufs[0] + i);
+#pragma unroll 1
+  for (int j = 1; j < world; ++j) {
+    const float4 v = ld_peer_v4(bufs[j] + i);
+    a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+  }
+  return a;
+}
+
+DTM_DEVICE void shard_range(int lo, int hi, int rank, int world, int& s_lo, int& s_hi) {
+  const int n = hi - lo;
+  int per = (n + world - 1) / world;
+  per = (per + 63) / 64 * 64;
+  s_lo = min(hi, lo + rank * per);
+  s_hi = min(hi, s_lo + per);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512, 1)
+fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cfg, dtm_train_state* __restrict__ st,
+                              int lo, int hi, float* __restrict__ slot0, float* __restrict__ slot1,
+                              float* __restrict__ ema, __nv_bfloat16* __restrict__ w_bf16, CommCtrl* __restrict__ ctrl,
+                              int do_finish) {
+  const int N = ctx.world, r = ctx.rank;
+  const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
+  const UpdateScalars u = make_update_scalars(cfg, st, 1.0f / static_cast<float>(N));
+  float* w_local = ctx.w[r];
+  float* g_local = ctx.grad[r];
+  (void)g_local;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nthreads = gridDim.x * blockDim.x;
+
+  // ---- while peers are still finishing their backward pass: sum of squares of the decayed variables (the
+  //      l2_loss terms of the loss value use the weights of the step in flight, mnist_input.py:113)
+  {
+    __shared__ float s_wl[DTM_MAX_SEGMENTS];
+    if (threadIdx.x < DTM_MAX_SEGMENTS) s_wl[threadIdx.x] = 0.0f;
+    __syncthreads();
+    bool any = false;
+    for (int s = 0; s < cfg.n_segments; ++s) {
+      if (cfg.seg_wd[s] == 0.0f) continue;
+      const int a = max(lo, cfg.seg_offset[s]), b = min(hi, cfg.seg_offset[s + 1]);
+      if (a >= b) continue;
+      any = true;
+      float sq = 0.0f;
+      for (int i = a + tid * 4; i < b; i += nthreads * 4) {
+        const float4 v = *reinterpret_cast<const float4*>(w_local + i);
+        sq += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+      }
+      sq = warp_sum(sq);
+      if (lane_id() == 0 && sq != 0.0f) atomicAdd(&s_wl[s], sq);
+    }
+    __syncthreads();
+    if (any && threadIdx.x < cfg.n_segments && s_wl[threadIdx.x] != 0.0f) atomicAdd(&st->wl_sum[threadIdx.x], s_wl[threadIdx.x]);
+  }
+
+  // ---- barrier A: every rank's gradients are complete
+  cross_gpu_barrier(ctx, ctrl, e0 + 1);
+
+  // ---- reduce-scatter + optimizer on my shard + all-gather of the new weights
+  int s_lo, s_hi;
+  shard_range(lo, hi, r, N, s_lo, s_hi);
+  for (int i = s_lo + tid * 4; i < s_hi; i += nthreads * 4) {
+    const float4 g = reduce_peers(ctx.grad, N, i);
+    const int seg = segment_of(cfg, i);
+    const float wd = cfg.seg_wd[seg];
+    const float4 wv = *reinterpret_cast<const float4*>(w_local + i);
+    float4 o;
+    o.x = update_element(cfg, u, wv.x, g.x, wd, slot0, slot1, ema, i + 0);
+    o.y = update_element(cfg, u, wv.y, g.y, wd, slot0, slot1, ema, i + 1);
+    o.z = update_element(cfg, u, wv.z, g.z, wd, slot0, slot1, ema, i + 2);
+    o.w = update_element(cfg, u, wv.w, g.w, wd, slot0, slot1, ema, i + 3);
+    *reinterpret_cast<float4*>(w_local + i) = o;
+#pragma unroll 1
+    for (int j = 1; j < N; ++j) {   // start with the next rank so that the N ranks do not all hit the same peer
+      const int p = (r + j) % N;
+      st_peer_v4(ctx.w[p] + i, o);
+    }
+  }
+
+  // ---- barrier B: all shards of the new weights have landed everywhere, nobody reads my gradients any more
+  cross_gpu_barrier(ctx, ctrl, e0 + 2);
+
+  // ---- local pass over the whole bucket: bf16 shadow weights, clear accumulated gradients
+  for (int i = lo + tid * 4; i < hi; i += nthreads * 4) {
+    const float4 v = *reinterpret_cast<const float4*>(w_local + i);
+    *reinterpret_cast<uint2*>(w_bf16 + i) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+    if (cfg.seg_zero_grad[segment_of(cfg, i)]) *reinterpret_cast<float4*>(g_local + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+
+  __threadfence();
+  __syncthreads();
+  __shared__ unsigned int s_last;
+  if (threadIdx.x == 0) s_last = (atomicAdd(&ctrl->ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    __threadfence();
+    ctrl->ticket = 0;
+    st_release_gpu(&ctrl->epoch, e0 + 2);
+    if (do_finish) {
+      const float lr_plain = cfg.base_lr * powf(cfg.decay_rate, cfg.decay_steps > 0 ? floorf((float)(st->global_step / cfg.decay_steps)) : 0.f);
+      finish_step(cfg, st, lr_plain);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Stand-alone all-reduce (sum) of n floats at element offset `off` of the symmetric buffer `buf`.
+//   mode 0 (one-shot): out[i] = sum_j buf_j[i], every rank reads all peers.
+//   mode 1 (two-shot): shard owner reduces and writes the sum back into every rank's buf (in place); out = buf.
+__global__ void __launch_bounds__(512, 1)
+allreduce_kernel(const dtm_peer_ctx ctx, float* const* __restrict__ bufs, int off, int n, float* __restrict__ out,
+                 int mode, CommCtrl* __restrict__ ctrl) {
+  const int N = ctx.world, r = ctx.rank;
+  const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nthreads = gridDim.x * blockDim.x;
+  cross_gpu_barrier(ctx, ctrl, e0 + 1);
+  if (mode == 0) {
+    for (int i = tid * 4; i < n; i += nthreads * 4) {
+      const float4 a = reduce_peers(bufs, N, off + i);
+      *reinterpret_cast<float4*>(out + i) = a;
+    }
+  } else {
+    int s_lo, s_hi;
+    shard_range(0, n, r, N, s_lo, s_hi);
+    for (int i = s_lo + tid * 4; i < s_hi; i += nthreads * 4) {
+      const float4 a = reduce_peers(bufs, N, off + i);
+#pragma unroll 1
+      for (int j = 0; j < N; ++j) st_peer_v4(bufs[(r + j) % N] + off + i, a);
+    }
+  }
+  cross_gpu_barrier(ctx, ctrl, e0 + 2);
+  if (mode == 1 && out != bufs[r] + off)
+    for (int i = tid * 4; i < n; i += nthreads * 4)
+      *reinterpret_cast<float4*>(out + i) = *reinterpret_cast<const float4*>(bufs[r] + off + i);
+  __syncthreads();
+  __shared__ unsigned int s_last;
+  if (threadIdx.x == 0) { __threadfence(); s_last = (atomicAdd(&ctrl->ticket, 1u) == gridDim.x - 1) ? 1u : 0u; }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) { ctrl->ticket = 0; st_release_gpu(&ctrl->epoch, e0 + 2); }
+}
+
+// Every rank copies n floats (and optionally the training state) from the root's symmetric buffer.
+__global__ void __launch_bounds__(512, 1)
+broadcast_kernel(const dtm_peer_ctx ctx, float* const* __restrict__ bufs, int off, int n, int root, CommCtrl* __restrict__ ctrl) {
+  const int r = ctx.rank;
+  const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nthreads = gridDim.x * blockDim.x;
+  cross_gpu_barrier(ctx, ctrl, e0 + 1);
+  if (r != root)
+    for (int i = tid * 4; i < n; i += nthreads * 4)
+      *reinterpret_cast<float4*>(bufs[r] + off + i) = ld_peer_v4(bufs[root] + off + i);
+  cross_gpu_barrier(ctx, ctrl, e0 + 2);
+  __shared__ unsigned int s_last;
+  if (threadIdx.x == 0) { __threadfence(); s_last = (atomicAdd(&ctrl->ticket, 1u) == gridDim.x - 1) ? 1u : 0u; }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) { ctrl->ticket = 0; st_release_gpu(&ctrl->epoch, e0 + 2); }
+}
+
+template <typename Kernel, typename... Args>
+static int launch_cooperative(Kernel kern, int grid, int block, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  DTM_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, args...));
+  return 0;
+}
+
+static int comm_grid(size_t elems, int max_ctas = 0) {
+  // enough CTAs to keep 18 NVLinks busy, never more than one per SM (co-residency for the spin barriers)
+  size_t want = (elems / 4 + 511) / 512;
+  int cap = device_sm_count();
+  if (max_ctas > 0 && max_ctas < cap) cap = max_ctas;
+  if (want < 1) want = 1;
+  return static_cast<int>(want > static_cast<size_t>(cap) ? cap : want);
+}
+
+static int check_ctx(const dtm_peer_ctx* ctx) {
+  if (!ctx) return dtm_fail("comm: null context");
+  if (ctx->world < 1 || ctx->world > DTM_MAX_RANKS) return dtm_fail("comm: world size out of range");
+  if (ctx->rank < 0 || ctx->rank >= ctx->world) return dtm_fail("comm: bad rank");
+  return 0;
+}
+
+}  // namespace dtm
+
+// ---- symmetric memory (CUDA IPC) ----------------------------------------------------------------------------
+extern "C" int dtm_symm_alloc(size_t bytes, void** ptr, unsigned char* handle64) {
+  using namespace dtm;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (!ptr || !handle64 || bytes == 0) return dtm_fail("symm_alloc: bad arguments");
+  void* p = nullptr;
+  DTM_CUDA_OK(cudaMalloc(&p, bytes));
+  DTM_CUDA_OK(cudaMemset(p, 0, bytes));
+  cudaIpcMemHandle_t h;
+  DTM_CUDA_OK(cudaIpcGetMemHandle(&h, p));
+  memcpy(handle64, &h, 64);
+  *ptr = p;
+  return 0;
+}
+extern "C" int dtm_symm_open(const unsigned char* handle64, void** peer_ptr) {
+  using namespace dtm;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  DTM_CUDA_OK(cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+extern "C" int dtm_symm_close(void* peer_ptr) {
+  using namespace dtm;
+  DTM_CUDA_OK(cudaIpcCloseMemHandle(peer_ptr));
+  return 0;
+}
+extern "C" int dtm_symm_free(void* ptr) {
+  using namespace dtm;
+  DTM_CUDA_OK(cudaFree(ptr));
+  return 0;
+}
+
+// ---- collectives ------------------------------------------------------------------------------------------
+extern "C" int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_update_config* cfg, dtm_train_state* state,
+                                          int lo, int hi, float* slot0, float* slot1, float* ema, void* w_bf16, void* ctrl,
+                                          int do_finish, int max_ctas, void* stream) {
+  using namespace dtm;
+  if (int rc = check_ctx(ctx)) return rc;
+  if (!cfg || !state || !ctrl || !w_bf16) return dtm_fail("fused_allreduce_update: null argument");
+  if (lo < 0 || hi > cfg->total || lo >= hi || lo % 64 || hi % 64) return dtm_fail("fused_allreduce_update: bad element range");
+  if (cfg->optimizer == DTM_OPT_ADAM && (!slot0 || !slot1)) return dtm_fail("fused_allreduce_update: Adam needs both slots");
+  if (cfg->optimizer == DTM_OPT_MOMENTUM && !slot0) return dtm_fail("fused_allreduce_update: Momentum needs slot0");
+  return launch_cooperative(fused_allreduce_update_kernel, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
+                            static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
+                            static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish);
+}
+
+extern "C" int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, int off, int n, float* out, int mode, void* ctrl,
+                                 void* stream) {
+  using namespace dtm;
+  if (int rc = check_ctx(ctx)) return rc;
+  if (n <= 0 || n % 4 || off % 4) return dtm_fail("allreduce: n and offset must be positive multiples of 4");
+  if (mode != 0 && mode != 1) return dtm_fail("allreduce: mode 0 (one-shot) or 1 (two-shot)");
+  const size_t work = mode == 0 ? static_cast<size_t>(n) : static_cast<size_t>(n) / ctx->world + 1;
+  return launch_cooperative(allreduce_kernel, comm_grid(work), 512, static_cast<cudaStream_t>(stream), *ctx, bufs_dev, off, n, out,
+                            mode, static_cast<CommCtrl*>(ctrl));
+}
+
+extern "C" int dtm_broadcast_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, int off, int n, int root, void* ctrl, void* stream) {
+  using namespace dtm;
+  if (int rc = check_ctx(ctx)) return rc;
+  if (n <= 0 || n % 4 || off % 4) return dtm_fail("broadcast: n and offset must be positive multiples of 4");
+  if (root < 0 || root >= ctx->world) return dtm_fail("broadcast: bad root");
+  return launch_cooperative(broadcast_kernel, comm_grid(static_cast<size_t>(n)), 512, static_cast<cudaStream_t>(stream), *ctx,
+                            bufs_dev, off, n, root, static_cast<CommCtrl*>(ctrl));
+}

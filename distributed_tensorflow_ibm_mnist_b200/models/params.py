@@ -30,13 +30,13 @@ class FlatParams:
             self.index[v.name] = i
             off += _align(v.size)
         self.total = off
-        alloc = allocator or (lambda n, dtype: torch.zeros(n, dtype=dtype, device=self.device))
-        self.w = alloc(self.total, torch.float32)
-        self.grad = alloc(self.total, torch.float32)
-        self.slot0 = alloc(self.total, torch.float32) if with_slots >= 1 else None
-        self.slot1 = alloc(self.total, torch.float32) if with_slots >= 2 else None
-        self.ema = alloc(self.total, torch.float32) if with_ema else None
-        self.w_bf16 = alloc(self.total, torch.bfloat16)
+        alloc = allocator or (lambda n, dtype, name="": torch.zeros(n, dtype=dtype, device=self.device))
+        self.w = alloc(self.total, torch.float32, "w")
+        self.grad = alloc(self.total, torch.float32, "grad")
+        self.slot0 = alloc(self.total, torch.float32, "slot0") if with_slots >= 1 else None
+        self.slot1 = alloc(self.total, torch.float32, "slot1") if with_slots >= 2 else None
+        self.ema = alloc(self.total, torch.float32, "ema") if with_ema else None
+        self.w_bf16 = alloc(self.total, torch.bfloat16, "w_bf16")
 
     # ---- views ------------------------------------------------------------------------------------
     def _view(self, buf: torch.Tensor, name: str) -> torch.Tensor:

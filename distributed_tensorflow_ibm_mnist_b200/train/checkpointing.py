@@ -104,11 +104,17 @@ def checkpoint_prefix(train_dir: str, step: int) -> str:
     return os.path.join(train_dir, f"model.ckpt-{step}")
 
 
-def save_checkpoint(train_dir: str, engine, spec: ModelSpec, optimizer: str, *, num_shards: int = 1, max_to_keep: int = 5) -> str:
-    """Write ``model.ckpt-<global_step>`` + update the ``checkpoint`` state file; returns the prefix."""
+def save_checkpoint(train_dir: str, engine, spec: ModelSpec, optimizer: str, *, num_shards: int = 1, max_to_keep: int = 5,
+                    write: bool = True) -> str:
+    """Write ``model.ckpt-<global_step>`` + update the ``checkpoint`` state file; returns the prefix.
+
+    With a sharded engine (fused multi-GPU update) collecting the variables is a collective: every rank calls this,
+    only the chief passes ``write=True``."""
     variables = collect_variables(engine, spec, optimizer)
     step = int(variables["global_step"])
     prefix = checkpoint_prefix(train_dir, step)
+    if not write:
+        return prefix
     tb.write_bundle(prefix, variables, shard_assignment(list(variables), spec, num_shards), num_shards)
     st = cs.read_state(train_dir) or cs.CheckpointState()
     rel = os.path.basename(prefix)
@@ -192,12 +198,18 @@ class CheckpointSaver:
         self._last = time.time()
         self.saved: list[str] = []
 
-    def maybe_save(self, engine, force: bool = False) -> str | None:
-        now = time.time()
-        if not force and (self.save_secs is None or now - self._last < self.save_secs):
-            return None
-        self._last = now
+    def due(self) -> bool:
+        return self.save_secs is not None and time.time() - self._last >= self.save_secs
+
+    def save(self, engine, write: bool = True) -> str:
+        self._last = time.time()
         p = save_checkpoint(self.train_dir, engine, self.spec, self.optimizer, num_shards=self.num_shards,
-                            max_to_keep=self.max_to_keep)
-        self.saved.append(p)
+                            max_to_keep=self.max_to_keep, write=write)
+        if write:
+            self.saved.append(p)
         return p
+
+    def maybe_save(self, engine, force: bool = False) -> str | None:
+        if not force and not self.due():
+            return None
+        return self.save(engine)

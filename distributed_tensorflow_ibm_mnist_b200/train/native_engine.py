@@ -47,7 +47,13 @@ class NativeEngine:
         self._alloc_activations(keep_logits)
         self._graphs: dict[int, torch.cuda.CUDAGraph] = {}
         self._side = torch.cuda.Stream(device=self.device)
-        self._fork_ev = [torch.cuda.Event() for _ in range(4)]
+        self._comm_stream = torch.cuda.Stream(device=self.device)
+        self._fork_ev = [torch.cuda.Event() for _ in range(6)]
+        # gradient buckets in flat-buffer order: the fc/head variables (93 % of the bytes, ready right after the first
+        # backward GEMMs) and the conv variables (ready last).  With >1 rank bucket 0 is reduced + updated on its own
+        # stream while the conv backward still runs.
+        split = self.flat.offsets["local3/weights"]
+        self.buckets = [(split, self.flat.total), (0, split)]
         self.launches_per_step = 0
 
     # ------------------------------------------------------------------------------------------------
@@ -91,15 +97,25 @@ class NativeEngine:
             self.state.copy_(torch.frombuffer(bytearray(bytes(st)), dtype=torch.uint8).to(self.device))
         torch.cuda.synchronize(self.device)
 
+    @property
+    def sharded(self) -> bool:
+        """True when optimizer slots / EMA shadows are only valid on their owning rank (fused multi-GPU update)."""
+        return self.comm is not None and self.world > 1
+
     def params(self) -> dict[str, torch.Tensor]:
         return {k: v.cpu() for k, v in self.flat.to_dict().items()}
 
+    def _full(self, buf: torch.Tensor) -> dict[str, torch.Tensor]:
+        if self.sharded:   # collective: every rank must call
+            buf = self.comm.gather_sharded(buf, self.buckets)
+        return {v.name: buf[self.flat.offsets[v.name]:self.flat.offsets[v.name] + v.size].view(v.shape).cpu() for v in self.spec.variables}
+
     def ema_params(self) -> dict[str, torch.Tensor]:
-        return {k: v.cpu() for k, v in self.flat.ema_dict().items()}
+        return self._full(self.flat.ema)
 
     def slots(self) -> list[dict[str, torch.Tensor]]:
         n = {"sgd": 0, "momentum": 1, "adam": 2}[self.optimizer.lower()]
-        return [{k: v.cpu() for k, v in self.flat.slot_dict(i).items()} for i in range(n)]
+        return [self._full(self.flat.slot0 if i == 0 else self.flat.slot1) for i in range(n)]
 
     def gradients(self) -> dict[str, torch.Tensor]:
         return {k: v.cpu() for k, v in self.flat.grad_dict().items()}
@@ -134,7 +150,7 @@ class NativeEngine:
         if count is not None:
             count[0] += n
 
-    def _backward(self, x, count) -> None:
+    def _backward(self, x, count, with_comm: bool = True) -> None:
         s, f, B = self.spec, self.flat, self.B
         n = 0
         h = self.h2 if s.fc2 else self.h1
@@ -160,6 +176,17 @@ class NativeEngine:
             self._fork_ev[1].record(self._side)
         native.gemm_bf16(dy1, 0, f.weight_bf16("local3/weights"), 0, self.dp2, B, 3136, s.fc1,
                          epilogue=native.EPI_MASK_BF16, ref=self.p2); n += 1
+        overlap_comm = self.sharded and with_comm
+        if overlap_comm:
+            # bucket 0 (fc + head variables): all gradients are complete once the dW GEMM is done, and the last reader of
+            # the fc weights (the dP2 GEMM above) has been issued: reduce + update them now, beside the conv backward.
+            self._fork_ev[4].record(main)
+            self._comm_stream.wait_event(self._fork_ev[4])
+            self._comm_stream.wait_event(self._fork_ev[1])
+            with torch.cuda.stream(self._comm_stream):
+                lo, hi = self.buckets[0]
+                self.comm.fused_allreduce_update(self.cfg, self.state, f, lo, hi, finish=False, overlapped=True); n += 1
+                self._fork_ev[5].record(self._comm_stream)
         native.unpool2(self.dp2, self.arg2, self.act2, self.dz2, f.gradient("conv2/biases"), batch=B, lrn=s.lrn); n += 1
         # fork: conv2 wgrad runs beside dgrad -> conv1 wgrad
         self._fork_ev[2].record(main)
@@ -172,12 +199,15 @@ class NativeEngine:
                            channels=s.channels); n += 1
         main.wait_event(self._fork_ev[1])
         main.wait_event(self._fork_ev[3])
+        if overlap_comm:
+            main.wait_event(self._fork_ev[5])
         count[0] += n
 
     def _update(self, count) -> None:
         f = self.flat
-        if self.comm is not None and self.world > 1:
-            self.comm.fused_allreduce_update(self.cfg, self.state, f)
+        if self.sharded:
+            lo, hi = self.buckets[1]      # conv variables; bucket 0 was launched from inside the backward pass
+            self.comm.fused_allreduce_update(self.cfg, self.state, f, lo, hi, finish=True)
         else:
             native.fused_update(self.cfg, self.state, f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, grad_scale=1.0)
         count[0] += 1
@@ -237,7 +267,7 @@ class NativeEngine:
         """Forward + backward only (gradients left in the flat buffer); used by tests and the summaries."""
         count = [0]
         self._forward(self.x[slot], self.y[slot], training=True, state=self.eval_state, count=count)
-        self._backward(self.x[slot], count)
+        self._backward(self.x[slot], count, with_comm=False)
 
     def evaluate(self, slot: int = 0) -> tuple[float, float]:
         """Loss and accuracy of the staged batch without touching weights (the reference's "test" summaries)."""

@@ -111,7 +111,7 @@ class MonitoredTrainingLoop:
     """``with MonitoredTrainingLoop(...) as sess: while not sess.should_stop(): sess.run_step()``."""
 
     def __init__(self, engine, source, *, hooks=(), is_chief=True, saver=None, task_id=0, feeder=None, log_every=100,
-                 verbose_steps=False, out=print):
+                 verbose_steps=False, out=print, group=None, save_poll_every=50):
         self.engine, self.source = engine, source
         self.hooks = list(hooks)
         self.is_chief, self.saver, self.task_id = is_chief, saver, task_id
@@ -121,6 +121,11 @@ class MonitoredTrainingLoop:
         self.start_step = int(engine.metrics()["global_step"])
         self.log_every, self.verbose_steps, self.out = log_every, verbose_steps, out
         self._t0 = None
+        # A sharded engine (fused multi-GPU update) needs every rank to take part in assembling a checkpoint, so the
+        # chief's time-based decision is broadcast at fixed step intervals and all ranks act on it together.
+        self.group = group
+        self.collective_saves = bool(getattr(engine, "sharded", False)) and group is not None and saver is not None
+        self.save_poll_every = max(1, save_poll_every)
 
     # the global step advances by exactly one per synchronous step, so the host can track it without a device read
     @property
@@ -148,13 +153,24 @@ class MonitoredTrainingLoop:
         self.local_steps += 1
         for h in self.hooks:
             h.after_run(self.ctx)
-        if self.is_chief and self.saver is not None:
+        if self.collective_saves:
+            if self.local_steps % self.save_poll_every == 0 and self._agree(self.is_chief and self.saver.due()):
+                self.saver.save(self.engine, write=self.is_chief)
+        elif self.is_chief and self.saver is not None:
             self.saver.maybe_save(self.engine)
         if self.verbose_steps:           # the reference prints "training" and the step every iteration (main.py:149-150)
             self.out("training")
             self.out(self.local_steps - 1)
         if self.log_every and self.local_steps % self.log_every == 0:
             self.out("%d steps executed on worker %d." % (self.local_steps, self.task_id))
+
+    def _agree(self, flag: bool) -> bool:
+        """The chief's decision, known to every rank."""
+        import torch.distributed as dist
+
+        box = [bool(flag)]
+        dist.broadcast_object_list(box, src=0, group=self.group)
+        return bool(box[0])
 
     def summary_tensors(self) -> dict:
         eng = self.engine
@@ -178,7 +194,9 @@ class MonitoredTrainingLoop:
         if exc_type is None:
             for h in self.hooks:
                 h.end(self)
-            if self.is_chief and self.saver is not None:
+            if self.collective_saves:
+                self.saver.save(self.engine, write=self.is_chief)
+            elif self.is_chief and self.saver is not None:
                 self.saver.maybe_save(self.engine, force=True)
         self.out("%d steps executed on worker %d." % (self.local_steps, self.task_id))
         return False

@@ -65,6 +65,16 @@ typedef struct dtm_update_config {
   int seg_zero_grad[DTM_MAX_SEGMENTS]; /* 1: gradient is accumulated with atomics and must be cleared after use */
 } dtm_update_config;
 
+/* Peer-memory communication context, passed to kernels by value: base pointers of every rank's symmetric buffers
+ * (flat gradient, flat fp32 weights, barrier flags), obtained through CUDA IPC (dtm_symm_*). */
+#define DTM_MAX_RANKS 8
+typedef struct dtm_peer_ctx {
+  int rank, world;
+  float* grad[DTM_MAX_RANKS];
+  float* w[DTM_MAX_RANKS];
+  unsigned int* flags[DTM_MAX_RANKS]; /* DTM_MAX_RANKS epochs per rank; slot r of rank p is written by rank r */
+} dtm_peer_ctx;
+
 /* ---- runtime ---------------------------------------------------------------------------------- */
 const char* dtm_last_error(void);
 int dtm_abi_version(void);
@@ -142,6 +152,28 @@ int dtm_tensor_stats(const void* x, size_t n, int is_bf16, float* out6, void* sc
 int dtm_histogram(const void* x, size_t n, int is_bf16, const double* limits, int nbins, float* counts, void* stream);
 /* host helper: CRC-32C of a host buffer, continuing from `crc` (TFRecord / checkpoint / event-file codecs). */
 uint32_t dtm_crc32c(const char* data, size_t n, uint32_t crc);
+
+/* ---- peer-memory communication (replaces the reference's gRPC parameter-server traffic: main.py:58-60, :80-93;
+ *      mnist_input.py:262-267) ------------------------------------------------------------------------------------ */
+/* Symmetric memory: cudaMalloc + zero-fill + CUDA IPC handle (64 bytes, host memory) to be exchanged between the
+ * ranks of one node; dtm_symm_open maps a peer's allocation into this process. */
+int dtm_symm_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+int dtm_symm_open(const unsigned char* handle64, void** peer_ptr);
+int dtm_symm_close(void* peer_ptr);
+int dtm_symm_free(void* ptr);
+/* One kernel: cross-GPU barrier, reduce-scatter of grad[lo:hi) over peer loads, scale 1/N + weight decay + optimizer
+ * + EMA on this rank's shard, all-gather of the new fp32 weights by peer stores, barrier, bf16 shadow + gradient
+ * clearing; with do_finish the step bookkeeping of dtm_fused_update.  `ctrl` = 16 bytes of zero-initialised device
+ * memory per communicator.  max_ctas > 0 caps the grid (use when the kernel overlaps with compute kernels).
+ * All ranks must issue the same sequence of collectives. */
+int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_update_config* cfg, dtm_train_state* state, int lo, int hi,
+                               float* slot0, float* slot1, float* ema, void* w_bf16, void* ctrl, int do_finish, int max_ctas,
+                               void* stream);
+/* fp32 sum over ranks of n floats at element offset off of a symmetric buffer (bufs_dev: device array of the N base
+ * pointers).  mode 0 one-shot -> out (local); mode 1 two-shot, in place in every rank's buffer (+ copy to out). */
+int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, int off, int n, float* out, int mode, void* ctrl,
+                      void* stream);
+int dtm_broadcast_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, int off, int n, int root, void* ctrl, void* stream);
 
 #ifdef __cplusplus
 }

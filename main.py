@@ -188,6 +188,9 @@ def train():
 
     hooks = [trainer.StopAtStepHook(last_step=max_steps), trainer.NanLossHook()]
     saver = None
+    if getattr(engine, "sharded", False):   # every rank helps assembling checkpoints; only the chief writes them
+        saver = checkpointing.CheckpointSaver(FLAGS.train_dir, spec, opt.kind, save_secs=hp.save_checkpoint_secs,
+                                              num_shards=max(1, cluster.num_ps), max_to_keep=hp.max_to_keep)
     if is_chief:
         log_dir = os.path.join(FLAGS.train_dir, "log")
         monitor = monitor_cb.CMonitor(log_dir, test_interval, max_steps)
@@ -208,7 +211,7 @@ def train():
                                               num_shards=max(1, cluster.num_ps), max_to_keep=hp.max_to_keep)
 
     with trainer.MonitoredTrainingLoop(engine, source, hooks=hooks, is_chief=is_chief, saver=saver, task_id=role.task_id,
-                                       feeder=feeder, verbose_steps=FLAGS.verbose_steps) as sess:
+                                       feeder=feeder, verbose_steps=FLAGS.verbose_steps, group=group) as sess:
         while not sess.should_stop():
             sess.run_step()
     m = engine.metrics()
