@@ -151,3 +151,79 @@ extern "C" int dtm_histogram(const void* x, size_t n, int is_bf16, const double*
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// dtm_tensor_stats_static: the same reduction for callers that have no device memory to hand over as scratch.
+//
+// Who that is: a monitoring or diagnostics hook that fires while every byte of the GPU is already spoken for (the
+// trainer sized its buffers to the card, or an out-of-memory / NaN post-mortem is being written), a watcher thread
+// that must not call cudaMalloc because that call can synchronise the whole device and stall the very training
+// streams it observes, or a plain-C host (this ABI works without PyTorch) that has no device allocator of its own.
+//
+// Instead of a caller-provided workspace the per-CTA partials live in the file-scope array below.  It is part of the
+// library image, so every GPU that loads libdtm_b200 carries these 16 KiB until the process exits — hence the cap.
+// Size limit: the partials of dtm_tensor_stats for n elements must fit, i.e. n <= DTM_STATS_STATIC_MAX_ELEMS;
+// larger tensors are refused (use dtm_tensor_stats with your own scratch).
+//
+// On the host, `g_stats_static_scratch` is only a stand-in symbol, not a device address; the address a kernel can use is
+// obtained once per device with cudaGetSymbolAddress while that device is current.  That look-up happens inside the
+// first call made on each device, so make that first call before starting any stream capture.
+//
+// All calls on a device share the one array: two calls whose kernels may run at the same time (different streams,
+// different threads) race on the partials and on the ticket and return garbage — serialise them.  The array keeps
+// whatever the previous call left behind; the only part that has to start at zero is the 64-byte ticket header, and
+// the entry point clears it on the caller's stream before every launch, so a call that died half-way cannot poison
+// the next one.  Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+// ---------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+#define DTM_STATS_STATIC_SCRATCH_BYTES 16384
+
+static __device__ __align__(256) unsigned char g_stats_static_scratch[DTM_STATS_STATIC_SCRATCH_BYTES];
+
+namespace dtm {
+
+constexpr size_t ST_STATIC_MAX_BLOCKS = (DTM_STATS_STATIC_SCRATCH_BYTES - ST_HEADER) / sizeof(StatPartial);   // 510
+constexpr size_t ST_STATIC_MAX_ELEMS = ST_STATIC_MAX_BLOCKS * ST_THREADS * 8;                               // 1 044 480
+
+static_assert(DTM_STATS_STATIC_MAX_ELEMS == ST_STATIC_MAX_ELEMS, "header constant out of sync with the kernel geometry");
+
+// Device address of the static scratch for the *current* device, resolved on first use per device.
+static int static_scratch_address(void** out) {
+  static std::mutex mu;
+  static void* addr[64] = {};
+  int dev = -1;
+  DTM_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return dtm_fail("tensor_stats_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    DTM_CUDA_OK(cudaGetSymbolAddress(&p, g_stats_static_scratch));
+    if (!p) return dtm_fail("tensor_stats_static: cudaGetSymbolAddress returned a null address");
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return 0;
+}
+
+}  // namespace dtm
+
+extern "C" int dtm_tensor_stats_static(const void* x, size_t n, int is_bf16, float* out6, void* stream) {
+  using namespace dtm;
+  if (n == 0) return dtm_fail("tensor_stats_static: empty tensor");
+  if (!x || !out6) return dtm_fail("tensor_stats_static: null input or output pointer");
+  if (n > ST_STATIC_MAX_ELEMS || dtm_tensor_stats_scratch_bytes(n) > DTM_STATS_STATIC_SCRATCH_BYTES)
+    return dtm_fail("tensor_stats_static: tensor too large for the built-in 16 KiB scratch (limit 1044480 elements); "
+                    "call dtm_tensor_stats with a caller-provided scratch buffer instead");
+  void* scratch = nullptr;
+  if (int rc = static_scratch_address(&scratch)) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  DTM_CUDA_OK(cudaMemsetAsync(scratch, 0, ST_HEADER, s));   // the ticket must start at zero whatever ran before
+  const int grid = stats_grid(n);
+  if (is_bf16)
+    tensor_stats_kernel<__nv_bfloat16><<<grid, ST_THREADS, 0, s>>>(static_cast<const __nv_bfloat16*>(x), n, out6, static_cast<uint8_t*>(scratch));
+  else
+    tensor_stats_kernel<float><<<grid, ST_THREADS, 0, s>>>(static_cast<const float*>(x), n, out6, static_cast<uint8_t*>(scratch));
+  DTM_CUDA_OK(cudaGetLastError());
+  return 0;
+}

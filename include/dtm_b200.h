@@ -148,6 +148,15 @@ int dtm_state_init(dtm_train_state* state, long long global_step, float beta1, f
  * (the kernel leaves them zero again); calls sharing one scratch buffer must not overlap on the GPU. */
 size_t dtm_tensor_stats_scratch_bytes(size_t n);
 int dtm_tensor_stats(const void* x, size_t n, int is_bf16, float* out6, void* scratch, size_t scratch_bytes, void* stream);
+/* Allocation-free variant of dtm_tensor_stats (no counterpart in the reference).  For callers that cannot hand over
+ * device scratch: hooks that run when the GPU's memory is fully committed, watcher threads that must not call
+ * cudaMalloc (it can synchronise the device and stall the streams being watched), plain-C hosts without a device
+ * allocator.  The partials live in a 16 KiB array inside the library image (held by every GPU that loads the library
+ * until process exit), which limits n to DTM_STATS_STATIC_MAX_ELEMS elements; larger inputs are rejected with an error.
+ * The first call on each device resolves the array's device address (make that call before any stream capture).
+ * Calls share the array: do not let two of them overlap on one GPU. */
+#define DTM_STATS_STATIC_MAX_ELEMS 1044480
+int dtm_tensor_stats_static(const void* x, size_t n, int is_bf16, float* out6, void* stream);
 /* counts[nbins] (float, accumulated) over the sorted bucket limits (device doubles), TensorFlow histogram rule. */
 int dtm_histogram(const void* x, size_t n, int is_bf16, const double* limits, int nbins, float* counts, void* stream);
 /* host helper: CRC-32C of a host buffer, continuing from `crc` (TFRecord / checkpoint / event-file codecs). */
