@@ -185,16 +185,13 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   // ---- reduce-scatter + optimizer on my shard + all-gather of the new weights
   int s_lo, s_hi;
   shard_range(lo, hi, r, N, s_lo, s_hi);
+  int seg = 0;
   for (int i = s_lo + tid * 4; i < s_hi; i += nthreads * 4) {
     const float4 g = reduce_peers(ctx.grad, N, i);
-    const int seg = segment_of(cfg, i);
+    seg = segment_advance(cfg, seg, i);
     const float wd = cfg.seg_wd[seg];
     const float4 wv = *reinterpret_cast<const float4*>(w_local + i);
-    float4 o;
-    o.x = update_element(cfg, u, wv.x, g.x, wd, slot0, slot1, ema, i + 0);
-    o.y = update_element(cfg, u, wv.y, g.y, wd, slot0, slot1, ema, i + 1);
-    o.z = update_element(cfg, u, wv.z, g.z, wd, slot0, slot1, ema, i + 2);
-    o.w = update_element(cfg, u, wv.w, g.w, wd, slot0, slot1, ema, i + 3);
+    const float4 o = update_vec4(cfg, u, wv, g, wd, slot0, slot1, ema, i);
     *reinterpret_cast<float4*>(w_local + i) = o;
 #pragma unroll 1
     for (int j = 1; j < N; ++j) {   // start with the next rank so that the N ranks do not all hit the same peer
@@ -207,10 +204,13 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   cross_gpu_barrier(ctx, ctrl, e0 + 2);
 
   // ---- local pass over the whole bucket: bf16 shadow weights, clear accumulated gradients
+  seg = 0;
   for (int i = lo + tid * 4; i < hi; i += nthreads * 4) {
     const float4 v = *reinterpret_cast<const float4*>(w_local + i);
     *reinterpret_cast<uint2*>(w_bf16 + i) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
-    if (cfg.seg_zero_grad[segment_of(cfg, i)]) *reinterpret_cast<float4*>(g_local + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    seg = segment_advance(cfg, seg, i);
+    if (seg == cfg.pack_seg) pack_conv2_vec4(cfg, i - cfg.seg_offset[seg], v);
+    if (cfg.seg_zero_grad[seg]) *reinterpret_cast<float4*>(g_local + i) = make_float4(0.f, 0.f, 0.f, 0.f);
   }
 
   __threadfence();

@@ -150,6 +150,29 @@ DTM_DEVICE void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same with the accumulate flag known at compile time (no predicate set-up in the issue loop).
+template <bool ACCUMULATE>
+DTM_DEVICE void umma_f16_c(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc) {
+  if (ACCUMULATE) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.eq.b32 p, 0, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, 0, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc)
+        : "memory");
+  }
+}
 // Arrive on an mbarrier once all previously issued tcgen05.mma of this thread have completed.
 DTM_DEVICE void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
@@ -199,6 +222,21 @@ DTM_DEVICE uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint3
   d |= static_cast<uint64_t>(1) << 46;  // descriptor version (Blackwell)
   d |= static_cast<uint64_t>(swizzle & 7u) << 61;
   return d;
+}
+
+// Descriptor arithmetic for issue loops.  Building a 64-bit descriptor from scratch costs ~20 dependent ALU ops, and the
+// single MMA-issuing thread executes them back to back: that, not the tensor core, bounds the issue rate.  The start
+// address occupies the low 14 bits of the low word, so moving an operand by a (compile-time) byte offset is one
+// 32-bit add on a pre-built base; the high word never changes.
+struct UmmaDescBase {
+  uint32_t lo, hi;
+};
+DTM_DEVICE UmmaDescBase umma_desc_base(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t swizzle) {
+  const uint64_t d = umma_smem_desc(smem_addr, lbo_bytes, sbo_bytes, swizzle);
+  return UmmaDescBase{static_cast<uint32_t>(d), static_cast<uint32_t>(d >> 32)};
+}
+DTM_DEVICE uint64_t umma_desc_at(const UmmaDescBase& b, int byte_offset) {
+  return (static_cast<uint64_t>(b.hi) << 32) | static_cast<uint64_t>(b.lo + static_cast<uint32_t>(byte_offset >> 4));
 }
 
 // 32-bit instruction descriptor for kind::f16 with bf16 A/B and fp32 D.

@@ -22,13 +22,17 @@ constexpr int DG_IMG_BYTES = plane_image_bytes(DG_CO);   // 32768
 constexpr int DG_BUFS = 2;
 constexpr int DG_SMEM = DG_W_BYTES + PL_GUARD_BYTES + DG_BUFS * DG_IMG_BYTES + PL_GUARD_BYTES + 128;
 
+// Like the forward kernel, the epilogue (TMEM read, activation fetch, mask, store) is a latency chain: without LRN two
+// warps share each TMEM lane quadrant (16 of the 32 channels each); LRN backward needs all 32 channels in one thread.
+template <bool LRN> struct DgEpi { static constexpr int WARPS = LRN ? 4 : 8; static constexpr int CH = LRN ? 32 : 16; };
+
 template <bool LRN>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(128 + 32 * DgEpi<LRN>::WARPS, 1)
 conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* __restrict__ w2,
-                   const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ pool_raw, int batch,
+                   const uint8_t* __restrict__ w_packed, const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ pool_raw, int batch,
                    __nv_bfloat16* __restrict__ dpool1) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t img_full[DG_BUFS], img_empty[DG_BUFS], acc_full[2], acc_empty[2];
+  __shared__ uint64_t img_full[DG_BUFS], img_empty[DG_BUFS], acc_full[2], acc_empty[2], w_full;
   __shared__ uint32_t tmem_slot;
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -41,7 +45,8 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
 
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < DG_BUFS; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 32 * DgEpi<LRN>::WARPS); }
+    mbar_init(&w_full, 1);
     fence_mbar_init();
   }
   if (warp == 2) { tmem_alloc(&tmem_slot, 128); tmem_relinquish(); }
@@ -50,7 +55,7 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
     for (int i = threadIdx.x * 16; i < 2 * PL_GUARD_BYTES + DG_BUFS * DG_IMG_BYTES; i += blockDim.x * 16)
       *reinterpret_cast<uint4*>(s_guard + i) = z;
   }
-  for (int chunk = threadIdx.x; chunk < (DG_K / 8) * DG_CI; chunk += blockDim.x) {
+  for (int chunk = threadIdx.x; w_packed == nullptr && chunk < (DG_K / 8) * DG_CI; chunk += blockDim.x) {
     const int k8 = chunk / DG_CI, ci = chunk % DG_CI;
     const int tap_f = k8 >> 3, co8 = k8 & 7;
     const uint4 v = *reinterpret_cast<const uint4*>(w2 + ((24 - tap_f) * DG_CI + ci) * DG_CO + co8 * 8);
@@ -65,6 +70,10 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
 
   if (warp == 0) {
     if (elect_one()) {
+      if (w_packed != nullptr) {
+        mbar_arrive_expect_tx(&w_full, DG_W_BYTES);
+        bulk_load_1d(s_w, w_packed, DG_W_BYTES, &w_full);
+      }
       int it = 0;
       for (int img = first; img < batch; img += stride, ++it) {
         const int b = it % DG_BUFS;
@@ -76,7 +85,8 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, DG_CI, false, false);
-      const uint32_t w_base = smem_u32(s_w);
+      const UmmaDescBase w_desc = umma_desc_base(smem_u32(s_w), DG_CI * 16, 128, UMMA_SWIZZLE_NONE);
+      if (w_packed != nullptr) mbar_wait(&w_full, 0, 24);
       int it = 0;
       for (int img = first; img < batch; img += stride, ++it) {
         const int b = it % DG_BUFS;
@@ -84,20 +94,20 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
         mbar_wait(&acc_empty[a], ((it >> 1) & 1) ^ 1, 21);
         mbar_wait(&img_full[b], (it / DG_BUFS) & 1, 22);
         tc_fence_after();
-        const uint32_t img_base = smem_u32(s_img + b * DG_IMG_BYTES);
+        const UmmaDescBase a_base = umma_desc_base(smem_u32(s_img + b * DG_IMG_BYTES), PL_PLANE_BYTES, 128, UMMA_SWIZZLE_NONE);
 #pragma unroll 1
         for (int t = 0; t < 2; ++t) {
           const uint32_t d_tmem = tmem_base + a * 64 + t * 32;
-#pragma unroll 1
+          const int tile_off = t * 128 * 16;
+#pragma unroll
           for (int tap = 0; tap < 25; ++tap) {
-            const int kh = tap / 5, kw = tap % 5;
-            const uint32_t a_addr = img_base + (t * 128 + kh * PL_GRID + kw - 2) * 16;
-            const uint32_t b_addr = w_base + tap * 8 * (DG_CI * 16);
+            const int a_off = ((tap / 5) * PL_GRID + (tap % 5) - 2) * 16;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const uint64_t da = umma_smem_desc(a_addr + j * 2 * PL_PLANE_BYTES, PL_PLANE_BYTES, 128, UMMA_SWIZZLE_NONE);
-              const uint64_t db = umma_smem_desc(b_addr + j * 2 * (DG_CI * 16), DG_CI * 16, 128, UMMA_SWIZZLE_NONE);
-              umma_f16(d_tmem, da, db, idesc, (tap | j) ? 1u : 0u);
+              const uint64_t da = umma_desc_at(a_base, tile_off + a_off + j * 2 * PL_PLANE_BYTES);
+              const uint64_t db = umma_desc_at(w_desc, (tap * 8 + j * 2) * (DG_CI * 16));
+              if (tap == 0 && j == 0) umma_f16_c<false>(d_tmem, da, db, idesc);
+              else                    umma_f16_c<true>(d_tmem, da, db, idesc);
             }
           }
         }
@@ -106,7 +116,9 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
       }
     }
   } else if (warp >= 4) {
+    constexpr int CH = DgEpi<LRN>::CH;
     const uint32_t q = warp & 3;
+    const int c0 = LRN ? 0 : static_cast<int>((warp - 4) >> 2) * 16;
     const int w_px = lane & 15, h_sub = lane >> 4;
     int it = 0;
     for (int img = first; img < batch; img += stride, ++it) {
@@ -117,18 +129,26 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
       for (int t = 0; t < 2; ++t) {
         const int h = t * 8 + q * 2 + h_sub;
         const bool valid = h < IMG && w_px < IMG;
-        uint32_t r[32];
-        tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 64 + t * 32, r);
-        tmem_ld_wait();
-        if (!valid) continue;
-        float g[DG_CI];
+        float g[CH];
+        if (LRN) {
+          uint32_t r[32];
+          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 64 + t * 32, r);
+          tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < DG_CI; ++j) g[j] = __uint_as_float(r[j]);
-        float act[DG_CI];  // the activation whose sign gates the gradient (pooled conv1 output, pre-LRN)
+          for (int j = 0; j < CH; ++j) g[j] = __uint_as_float(r[j % 32]);
+        } else {
+          uint32_t r[16];
+          tmem_ld_x16(tmem_base + ((q * 32u) << 16) + a * 64 + t * 32 + c0, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < CH; ++j) g[j] = __uint_as_float(r[j % 16]);
+        }
+        if (!valid) continue;
+        float act[CH];  // the activation whose sign gates the gradient (pooled conv1 output, pre-LRN)
         if (LRN) {
           const uint4* src = reinterpret_cast<const uint4*>(pool_raw + (static_cast<size_t>(img) * (IMG * IMG) + h * IMG + w_px) * DG_CI);
 #pragma unroll
-          for (int c8 = 0; c8 < 4; ++c8) {
+          for (int c8 = 0; c8 < CH / 8; ++c8) {
             const uint4 u = src[c8];
             const uint32_t wds[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
@@ -137,39 +157,39 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
           // LRN backward (TF semantics): s_c = 1 + alpha*sum a^2 ; y_c = a_c s_c^-beta
           //   da_j = dy_j s_j^-beta - 2 alpha beta a_j * sum_{|c-j|<=4} dy_c a_c s_c^(-beta-1)
           const float alpha = 0.001f / 9.0f, beta = 0.75f;
-          float t1[DG_CI], sp[DG_CI];
+          float t1[CH], sp[CH];
 #pragma unroll
-          for (int c = 0; c < DG_CI; ++c) {
-            float s = 0.0f;
+          for (int c = 0; c < CH; ++c) {
+            float ss = 0.0f;
 #pragma unroll
             for (int d = -4; d <= 4; ++d)
-              if (c + d >= 0 && c + d < DG_CI) s += act[c + d] * act[c + d];
-            s = 1.0f + alpha * s;
-            const float p = __powf(s, -beta);
-            sp[c] = p;
-            t1[c] = g[c] * act[c] * p / s;
+              if (c + d >= 0 && c + d < CH) ss += act[c + d] * act[c + d];
+            ss = 1.0f + alpha * ss;
+            const float pw = __powf(ss, -beta);
+            sp[c] = pw;
+            t1[c] = g[c] * act[c] * pw / ss;
           }
 #pragma unroll
-          for (int j = 0; j < DG_CI; ++j) {
+          for (int j = 0; j < CH; ++j) {
             float acc = 0.0f;
 #pragma unroll
             for (int d = -4; d <= 4; ++d)
-              if (j + d >= 0 && j + d < DG_CI) acc += t1[j + d];
+              if (j + d >= 0 && j + d < CH) acc += t1[j + d];
             g[j] = g[j] * sp[j] - 2.0f * alpha * beta * act[j] * acc;
           }
         } else {
           const uint8_t* src = p1_planes + static_cast<size_t>(img) * plane_image_bytes(DG_CI);
 #pragma unroll
-          for (int c8 = 0; c8 < 4; ++c8) {
-            const uint4 u = *reinterpret_cast<const uint4*>(src + plane_offset(h, w_px, c8 * 8));
+          for (int c8 = 0; c8 < CH / 8; ++c8) {
+            const uint4 u = *reinterpret_cast<const uint4*>(src + plane_offset(h, w_px, c0 + c8 * 8));
             const uint32_t wds[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
             for (int i = 0; i < 4; ++i) { act[c8 * 8 + 2 * i] = bf16_lo(wds[i]); act[c8 * 8 + 2 * i + 1] = bf16_hi(wds[i]); }
           }
         }
-        uint4* dst = reinterpret_cast<uint4*>(dpool1 + (static_cast<size_t>(img) * (IMG * IMG) + h * IMG + w_px) * DG_CI);
+        uint4* dst = reinterpret_cast<uint4*>(dpool1 + (static_cast<size_t>(img) * (IMG * IMG) + h * IMG + w_px) * DG_CI + c0);
 #pragma unroll
-        for (int c8 = 0; c8 < 4; ++c8) {
+        for (int c8 = 0; c8 < CH / 8; ++c8) {
           float o[8];
 #pragma unroll
           for (int i = 0; i < 8; ++i) o[i] = act[c8 * 8 + i] > 0.0f ? g[c8 * 8 + i] : 0.0f;
@@ -188,8 +208,8 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
 
 }  // namespace dtm
 
-extern "C" int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, const void* p1_planes, const void* pool_raw,
-                               int batch, int lrn, void* dpool1, void* stream) {
+extern "C" int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, const void* packed, const void* p1_planes,
+                               const void* pool_raw, int batch, int lrn, void* dpool1, void* stream) {
   using namespace dtm;
   if (batch <= 0) return dtm_fail("conv2_dgrad: batch must be positive");
   if (lrn && !pool_raw) return dtm_fail("conv2_dgrad: LRN backward needs pool_raw");
@@ -203,8 +223,8 @@ extern "C" int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, cons
   }
   const int grid = min(batch, device_sm_count());
   auto launch = [&](auto kern) {
-    kern<<<grid, 256, DG_SMEM, s>>>(static_cast<const uint8_t*>(dz2_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
-                                    static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(pool_raw), batch,
+    kern<<<grid, lrn ? 256 : 384, DG_SMEM, s>>>(static_cast<const uint8_t*>(dz2_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
+                                    static_cast<const uint8_t*>(packed), static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(pool_raw), batch,
                                     static_cast<__nv_bfloat16*>(dpool1));
   };
   if (lrn) launch(conv2_dgrad_kernel<true>);

@@ -29,12 +29,18 @@ constexpr float LRN2_BIAS = 1.0f;
 constexpr float LRN2_ALPHA = 0.001f / 9.0f;
 constexpr float LRN2_BETA = 0.75f;
 
+// Epilogue width: the pooling/arg-max code is a long dependent chain (3 shuffles + compares per channel), and with one
+// epilogue warp per scheduler it, not the tensor core, set the kernel time (ncu: tensor pipe 24 % active).  Without
+// LRN the 64 channels split cleanly, so two warps share each TMEM lane quadrant (32 channels each, 8 epilogue warps);
+// LRN needs a pixel's whole channel vector in one thread and keeps the 4-warp layout.
+template <bool LRN> struct C2Epi { static constexpr int WARPS = LRN ? 4 : 8; static constexpr int CH = LRN ? 64 : 32; };
+
 template <bool LRN>
-__global__ void __launch_bounds__(256, 1)
-conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ w2, const float* __restrict__ bias,
-                 int batch, __nv_bfloat16* __restrict__ p2, uint8_t* __restrict__ argmax, __nv_bfloat16* __restrict__ act2) {
+__global__ void __launch_bounds__(128 + 32 * C2Epi<LRN>::WARPS, 1)
+conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ w2,
+                 const uint8_t* __restrict__ w_packed, const float* __restrict__ bias, int batch, __nv_bfloat16* __restrict__ p2, uint8_t* __restrict__ argmax, __nv_bfloat16* __restrict__ act2) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t img_full[C2_BUFS], img_empty[C2_BUFS], acc_full[2], acc_empty[2];
+  __shared__ uint64_t img_full[C2_BUFS], img_empty[C2_BUFS], acc_full[2], acc_empty[2], w_full;
   __shared__ uint32_t tmem_slot;
   __shared__ float s_bias[C2_OUT];
 
@@ -49,7 +55,8 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
   // ---- one-time setup -------------------------------------------------------------------------
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < C2_BUFS; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 32 * C2Epi<LRN>::WARPS); }
+    mbar_init(&w_full, 1);
     fence_mbar_init();
   }
   if (warp == 2) { tmem_alloc(&tmem_slot, 256); tmem_relinquish(); }
@@ -59,8 +66,9 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
     for (int i = threadIdx.x * 16; i < 2 * PL_GUARD_BYTES + C2_BUFS * C2_IMG_BYTES; i += blockDim.x * 16)
       *reinterpret_cast<uint4*>(s_guard + i) = z;
   }
-  // weights: TF layout [k = tap*32 + ci][n = co] (n contiguous) -> [k/8][n][k%8]
-  for (int chunk = threadIdx.x; chunk < (C2_K / 8) * C2_OUT; chunk += blockDim.x) {
+  // weights: TF layout [k = tap*32 + ci][n = co] (n contiguous) -> [k/8][n][k%8]; skipped when the caller supplies
+  // the packed image (dtm_conv2_pack_weights), which the producer then fetches with one 100 KiB bulk copy
+  for (int chunk = threadIdx.x; w_packed == nullptr && chunk < (C2_K / 8) * C2_OUT; chunk += blockDim.x) {
     const int k8 = chunk / C2_OUT, n = chunk % C2_OUT;
     uint32_t v[4];
 #pragma unroll
@@ -83,6 +91,10 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
   if (warp == 0) {
     // ---- producer: one 16 KiB bulk copy per image ------------------------------------------------
     if (elect_one()) {
+      if (w_packed != nullptr) {
+        mbar_arrive_expect_tx(&w_full, C2_W_BYTES);
+        bulk_load_1d(s_w, w_packed, C2_W_BYTES, &w_full);
+      }
       int it = 0;
       for (int img = first; img < batch; img += stride, ++it) {
         const int b = it % C2_BUFS;
@@ -95,7 +107,8 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
     // ---- MMA issuer ----------------------------------------------------------------------------
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, C2_OUT, false, false);
-      const uint32_t w_base = smem_u32(s_w);
+      const UmmaDescBase w_desc = umma_desc_base(smem_u32(s_w), C2_OUT * 16, 128, UMMA_SWIZZLE_NONE);
+      if (w_packed != nullptr) mbar_wait(&w_full, 0, 14);
       int it = 0;
       for (int img = first; img < batch; img += stride, ++it) {
         const int b = it % C2_BUFS;
@@ -103,20 +116,20 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
         mbar_wait(&acc_empty[a], ((it >> 1) & 1) ^ 1, 11);
         mbar_wait(&img_full[b], (it / C2_BUFS) & 1, 12);
         tc_fence_after();
-        const uint32_t img_base = smem_u32(s_img + b * C2_IMG_BYTES);
+        const UmmaDescBase a_base = umma_desc_base(smem_u32(s_img + b * C2_IMG_BYTES), PL_PLANE_BYTES, 128, UMMA_SWIZZLE_NONE);
 #pragma unroll 1
         for (int t = 0; t < 2; ++t) {
           const uint32_t d_tmem = tmem_base + a * 128 + t * 64;
-#pragma unroll 1
+          const int tile_off = t * 128 * 16;
+#pragma unroll
           for (int tap = 0; tap < 25; ++tap) {
-            const int kh = tap / 5, kw = tap % 5;
-            const uint32_t a_addr = img_base + (t * 128 + kh * PL_GRID + kw - 2) * 16;
-            const uint32_t b_addr = w_base + tap * 4 * (C2_OUT * 16);
+            const int a_off = ((tap / 5) * PL_GRID + (tap % 5) - 2) * 16;   // compile-time after unrolling
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
-              const uint64_t da = umma_smem_desc(a_addr + j * 2 * PL_PLANE_BYTES, PL_PLANE_BYTES, 128, UMMA_SWIZZLE_NONE);
-              const uint64_t db = umma_smem_desc(b_addr + j * 2 * (C2_OUT * 16), C2_OUT * 16, 128, UMMA_SWIZZLE_NONE);
-              umma_f16(d_tmem, da, db, idesc, (tap | j) ? 1u : 0u);
+              const uint64_t da = umma_desc_at(a_base, tile_off + a_off + j * 2 * PL_PLANE_BYTES);
+              const uint64_t db = umma_desc_at(w_desc, (tap * 4 + j * 2) * (C2_OUT * 16));
+              if (tap == 0 && j == 0) umma_f16_c<false>(d_tmem, da, db, idesc);
+              else                    umma_f16_c<true>(d_tmem, da, db, idesc);
             }
           }
         }
@@ -126,7 +139,9 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
     }
   } else if (warp >= 4) {
     // ---- epilogue ------------------------------------------------------------------------------
-    const uint32_t q = warp & 3;
+    constexpr int CH = C2Epi<LRN>::CH;     // channels handled by this warp
+    const uint32_t q = warp & 3;           // TMEM lane quadrant
+    const int c0 = LRN ? 0 : static_cast<int>((warp - 4) >> 2) * 32;   // first channel of this warp
     const int w_px = lane & 15;            // column inside the 16-wide grid
     const int h_sub = lane >> 4;           // 0/1: row inside the warp's row pair
     int it = 0;
@@ -140,49 +155,46 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
         const int ph = t * 4 + q, pw = w_px >> 1;    // pooled coordinates of its window
         const bool writer = (lane < 16) && ((lane & 1) == 0) && pw < 7 && ph < 7;
         const bool pixel_valid = h < IMG && w_px < IMG;
-        float v[C2_OUT];
-        {
+        float v[CH];
+#pragma unroll
+        for (int cb = 0; cb < CH; cb += 32) {
           uint32_t r[32];
-          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 128 + t * 64, r);
+          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 128 + t * 64 + c0 + cb, r);
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(__uint_as_float(r[j]) + s_bias[j], 0.0f);
-          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 128 + t * 64 + 32, r);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[32 + j] = fmaxf(__uint_as_float(r[j]) + s_bias[32 + j], 0.0f);
+          for (int j = 0; j < 32; ++j) v[cb + j] = fmaxf(__uint_as_float(r[j]) + s_bias[c0 + cb + j], 0.0f);
         }
         if (LRN) {
           // act2 keeps the post-ReLU activation (bf16) for the backward pass; LRN runs on the rounded values
 #pragma unroll
-          for (int j = 0; j < C2_OUT; ++j) v[j] = __bfloat162float(__float2bfloat16(v[j]));
+          for (int j = 0; j < CH; ++j) v[j] = __bfloat162float(__float2bfloat16(v[j]));
           if (pixel_valid) {
             uint4* dst = reinterpret_cast<uint4*>(act2 + (static_cast<size_t>(img) * (IMG * IMG) + h * IMG + w_px) * C2_OUT);
 #pragma unroll
-            for (int j = 0; j < C2_OUT; j += 8)
+            for (int j = 0; j < CH; j += 8)
               dst[j >> 3] = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
                                        pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
           }
-          float sq[C2_OUT];
+          float sq[CH];
 #pragma unroll
-          for (int j = 0; j < C2_OUT; ++j) sq[j] = v[j] * v[j];
-          float y[C2_OUT];
+          for (int j = 0; j < CH; ++j) sq[j] = v[j] * v[j];
+          float y[CH];
 #pragma unroll
-          for (int j = 0; j < C2_OUT; ++j) {
-            float s = 0.0f;
+          for (int j = 0; j < CH; ++j) {
+            float sum = 0.0f;
 #pragma unroll
             for (int d = -4; d <= 4; ++d)
-              if (j + d >= 0 && j + d < C2_OUT) s += sq[j + d];
-            y[j] = v[j] * __powf(LRN2_BIAS + LRN2_ALPHA * s, -LRN2_BETA);
+              if (j + d >= 0 && j + d < CH) sum += sq[j + d];
+            y[j] = v[j] * __powf(LRN2_BIAS + LRN2_ALPHA * sum, -LRN2_BETA);
           }
 #pragma unroll
-          for (int j = 0; j < C2_OUT; ++j) v[j] = y[j];
+          for (int j = 0; j < CH; ++j) v[j] = y[j];
         }
         // 2x2 max-pool across lanes l, l^1 (w+1), l^16 (h+1), l^17
-        __nv_bfloat16* p2_dst = p2 + (static_cast<size_t>(img) * 49 + ph * 7 + pw) * C2_OUT;
-        uint8_t* am_dst = argmax + (static_cast<size_t>(img) * 49 + ph * 7 + pw) * C2_OUT;
+        __nv_bfloat16* p2_dst = p2 + (static_cast<size_t>(img) * 49 + ph * 7 + pw) * C2_OUT + c0;
+        uint8_t* am_dst = argmax + (static_cast<size_t>(img) * 49 + ph * 7 + pw) * C2_OUT + c0;
 #pragma unroll
-        for (int j0 = 0; j0 < C2_OUT; j0 += 8) {
+        for (int j0 = 0; j0 < CH; j0 += 8) {
           float best[8];
           uint32_t arg_lo = 0, arg_hi = 0;
 #pragma unroll
@@ -219,11 +231,12 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
 
 }  // namespace dtm
 
-extern "C" int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const float* bias, int batch, int lrn, void* p2,
-                             void* argmax, void* act2, void* stream) {
+extern "C" int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const void* packed, const float* bias, int batch, int lrn,
+                             void* p2, void* argmax, void* act2, void* stream) {
   using namespace dtm;
   if (batch <= 0) return dtm_fail("conv2_fwd: batch must be positive");
   if (lrn && !act2) return dtm_fail("conv2_fwd: LRN needs the act2 buffer");
+  if (!w2_bf16 && !packed) return dtm_fail("conv2_fwd: needs weights (w2_bf16 or packed)");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   static bool configured = false;
   if (!configured) {
@@ -233,8 +246,8 @@ extern "C" int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const f
   }
   const int grid = min(batch, device_sm_count());
   auto args = [&](auto kern) {
-    kern<<<grid, 256, C2_SMEM, s>>>(static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(w2_bf16), bias,
-                                    batch, static_cast<__nv_bfloat16*>(p2), static_cast<uint8_t*>(argmax),
+    kern<<<grid, lrn ? 256 : 384, C2_SMEM, s>>>(static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
+                                    static_cast<const uint8_t*>(packed), bias, batch, static_cast<__nv_bfloat16*>(p2), static_cast<uint8_t*>(argmax),
                                     static_cast<__nv_bfloat16*>(act2));
   };
   if (lrn) args(conv2_fwd_kernel<true>);

@@ -23,6 +23,31 @@ constexpr int WG_STAGES = 3;
 constexpr int WG_SMEM = WG_STAGES * WG_STAGE_BYTES + 128;
 constexpr int WG_TAPS_Y0 = 13;
 
+// All MMAs of one image for this CTA's tap group.  Taps are unrolled up to the larger group (13) with a uniform
+// predicate for the 12-tap group, K steps (image rows) stay a loop: every descriptor is base + compile-time offset
+// + ks * 256 B.
+template <bool FIRST_IMAGE>
+DTM_DEVICE void issue_image(uint32_t tmem_base, const UmmaDescBase& dz_base, const UmmaDescBase& p1_base, int tap0, int ntaps,
+                            uint32_t idesc) {
+#pragma unroll 1
+  for (int ks = PL_ROW_OFF; ks < PL_GRID; ++ks) {   // one K step = one image row of 16 grid pixels
+    const uint64_t da = umma_desc_at(dz_base, ks * 256);
+    const bool first = FIRST_IMAGE && ks == PL_ROW_OFF;
+    // tap = tap0 + tl, tap0 in {0, 13}: (kh, kw) offsets differ between the two groups, so both tables are unrolled
+#pragma unroll
+    for (int tl = 0; tl < WG_TAPS_Y0; ++tl) {
+      if (tl < ntaps) {
+        const int tap_a = tl, tap_b = WG_TAPS_Y0 + tl;
+        const int off_a = (((tap_a / 5) - 2) * PL_GRID + (tap_a % 5) - 2) * 16;
+        const int off_b = (((tap_b / 5) - 2) * PL_GRID + (tap_b % 5) - 2) * 16;
+        const uint64_t db = umma_desc_at(p1_base, ks * 256 + (tap0 == 0 ? off_a : off_b));
+        if (first) umma_f16_c<false>(tmem_base + tl * WG_CI, da, db, idesc);
+        else       umma_f16_c<true>(tmem_base + tl * WG_CI, da, db, idesc);
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256, 1)
 conv2_wgrad_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __restrict__ dz2_planes, int batch,
                    float* __restrict__ dw2) {
@@ -80,21 +105,11 @@ conv2_wgrad_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __restr
         const int s = it % WG_STAGES;
         mbar_wait(&full_bar[s], (it / WG_STAGES) & 1, 31);
         tc_fence_after();
-        const uint32_t p1_base = smem_u32(smem + s * WG_STAGE_BYTES + PL_GUARD_BYTES);
-        const uint32_t dz_base = smem_u32(smem + s * WG_STAGE_BYTES + 2 * PL_GUARD_BYTES + WG_P1_BYTES);
-#pragma unroll 1
-        for (int ks = PL_ROW_OFF; ks < PL_GRID; ++ks) {   // one K step = one image row of 16 grid pixels
-          const uint64_t da = umma_smem_desc(dz_base + ks * 256, 128, PL_PLANE_BYTES, UMMA_SWIZZLE_NONE);
-          const uint32_t acc = (it > 0 || ks > PL_ROW_OFF) ? 1u : 0u;
-#pragma unroll 1
-          for (int tl = 0; tl < ntaps; ++tl) {
-            const int tap = tap0 + tl;
-            const int kh = tap / 5, kw = tap % 5;
-            const uint32_t b_addr = p1_base + ((ks + kh - 2) * PL_GRID + kw - 2) * 16;
-            const uint64_t db = umma_smem_desc(b_addr, 128, PL_PLANE_BYTES, UMMA_SWIZZLE_NONE);
-            umma_f16(tmem_base + tl * WG_CI, da, db, idesc, acc);
-          }
-        }
+        const UmmaDescBase p1_base = umma_desc_base(smem_u32(smem + s * WG_STAGE_BYTES + PL_GUARD_BYTES), 128, PL_PLANE_BYTES, UMMA_SWIZZLE_NONE);
+        const UmmaDescBase dz_base = umma_desc_base(smem_u32(smem + s * WG_STAGE_BYTES + 2 * PL_GUARD_BYTES + WG_P1_BYTES), 128,
+                                                    PL_PLANE_BYTES, UMMA_SWIZZLE_NONE);
+        if (it == 0) issue_image<true>(tmem_base, dz_base, p1_base, tap0, ntaps, idesc);
+        else         issue_image<false>(tmem_base, dz_base, p1_base, tap0, ntaps, idesc);
         umma_commit(&empty_bar[s]);
       }
       umma_commit(&done_bar);

@@ -20,11 +20,10 @@ namespace dtm {
 constexpr int BM = 128;
 constexpr int BN = 64;
 constexpr int BK = 64;
-constexpr int STAGES = 4;
 constexpr int UK = 16;  // UMMA K for 16-bit inputs
 constexpr uint32_t A_STAGE_BYTES = BM * BK * 2;
 constexpr uint32_t B_STAGE_BYTES = BN * BK * 2;
-constexpr uint32_t GEMM_SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 1024;  // + alignment slack
+constexpr uint32_t gemm_smem_bytes(int stages) { return stages * (A_STAGE_BYTES + B_STAGE_BYTES) + 1024; }  // + alignment slack
 
 struct GemmArgs {
   int M, N, K;
@@ -40,8 +39,11 @@ struct GemmArgs {
   const long long* step_ptr;    // device global_step, makes the dropout mask step dependent
 };
 
-template <bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(256, 2)
+// STAGES = 4: two CTAs per SM (grids larger than the machine, short K).  STAGES = 8: one CTA per SM with twice the
+// bytes in flight — when the grid does not fill the GPU (the fc forward: 64 tiles, K = 3136) the kernel is bound by
+// TMA round-trip latency per K block, and depth is the only lever.
+template <bool A_MN, bool B_MN, int STAGES>
+__global__ void __launch_bounds__(256, STAGES <= 4 ? 2 : 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const GemmArgs g) {
   extern __shared__ uint8_t smem_raw[];
@@ -116,18 +118,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const uint32_t ph = (i / STAGES) & 1;
         mbar_wait(&full_bar[s], ph, 2);
         tc_fence_after();
-        const uint32_t a_base = smem_u32(smem_a + s * A_STAGE_BYTES);
-        const uint32_t b_base = smem_u32(smem_b + s * B_STAGE_BYTES);
+        // K-major SW128: 8-row groups 1024 B apart, a K step of 16 elements is +32 B inside the row.
+        // MN-major SW128: swizzle atoms (64 elements of M/N) BK*128 B apart, 8-k groups 1024 B apart,
+        //                 a K step of 16 rows is +2048 B.
+        const UmmaDescBase a_base = umma_desc_base(smem_u32(smem_a + s * A_STAGE_BYTES), A_MN ? BK * 128 : 0, 1024, UMMA_SWIZZLE_128B);
+        const UmmaDescBase b_base = umma_desc_base(smem_u32(smem_b + s * B_STAGE_BYTES), B_MN ? BK * 128 : 0, 1024, UMMA_SWIZZLE_128B);
 #pragma unroll
         for (int j = 0; j < BK / UK; ++j) {
-          // K-major SW128: 8-row groups 1024 B apart, a K step of 16 elements is +32 B inside the row.
-          // MN-major SW128: swizzle atoms (64 elements of M/N) BK*128 B apart, 8-k groups 1024 B apart,
-          //                 a K step of 16 rows is +2048 B.
-          const uint64_t da = A_MN ? umma_smem_desc(a_base + j * (UK * 128), BK * 128, 1024, UMMA_SWIZZLE_128B)
-                                   : umma_smem_desc(a_base + j * (UK * 2), 0, 1024, UMMA_SWIZZLE_128B);
-          const uint64_t db = B_MN ? umma_smem_desc(b_base + j * (UK * 128), BK * 128, 1024, UMMA_SWIZZLE_128B)
-                                   : umma_smem_desc(b_base + j * (UK * 2), 0, 1024, UMMA_SWIZZLE_128B);
-          umma_f16(tmem_d, da, db, idesc, (i > 0 || j > 0) ? 1u : 0u);
+          const uint64_t da = umma_desc_at(a_base, j * (A_MN ? UK * 128 : UK * 2));
+          const uint64_t db = umma_desc_at(b_base, j * (B_MN ? UK * 128 : UK * 2));
+          if (j == 0) umma_f16(tmem_d, da, db, idesc, i > 0 ? 1u : 0u);
+          else        umma_f16_c<true>(tmem_d, da, db, idesc);
         }
         umma_commit(&empty_bar[s]);  // frees this smem stage once the MMAs above have read it
       }
@@ -228,18 +229,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 2) tmem_dealloc(tmem_d, BN);
 }
 
-template <bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, int splits, cudaStream_t s) {
-  auto kern = gemm_bf16_kernel<A_MN, B_MN>;
+template <bool A_MN, bool B_MN, int STAGES>
+static int launch_gemm_s(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, dim3 grid, cudaStream_t s) {
+  auto kern = gemm_bf16_kernel<A_MN, B_MN, STAGES>;
   static bool configured = false;
   if (!configured) {
-    DTM_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    DTM_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(STAGES)));
     configured = true;
   }
-  dim3 grid((g.N + BN - 1) / BN, (g.M + BM - 1) / BM, splits);
-  kern<<<grid, 256, GEMM_SMEM_BYTES, s>>>(ta, tb, g);
+  kern<<<grid, 256, gemm_smem_bytes(STAGES), s>>>(ta, tb, g);
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
+}
+
+template <bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, int splits, cudaStream_t s) {
+  dim3 grid((g.N + BN - 1) / BN, (g.M + BM - 1) / BM, splits);
+  const int tiles = grid.x * grid.y * grid.z;
+  if (tiles <= device_sm_count() && g.k_blocks_per_split > 8) return launch_gemm_s<A_MN, B_MN, 8>(ta, tb, g, grid, s);
+  return launch_gemm_s<A_MN, B_MN, 4>(ta, tb, g, grid, s);
 }
 
 }  // namespace dtm

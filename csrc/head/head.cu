@@ -16,65 +16,104 @@ namespace dtm {
 
 constexpr int NCLS = 10;
 
+constexpr int HF_CHUNK = 1024;     // hidden units staged per pass
+constexpr int HF_PITCH = NCLS + 1; // 11 floats per weight row: lane stride 11 words is a permutation of the 32 banks
+
 __global__ void __launch_bounds__(256)
 head_forward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, const float* __restrict__ w,
                     const float* __restrict__ bias, const int* __restrict__ labels, float grad_scale, float loss_scale,
                     float* __restrict__ logits_out, float* __restrict__ probs_out, float* __restrict__ dlogits,
                     dtm_train_state* __restrict__ state) {
-  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  __shared__ float s_w[HF_CHUNK * HF_PITCH];   // 44 KiB: the weight rows of the current chunk, shared by the CTA's 8 rows
+  __shared__ float s_loss[8], s_corr[8];
+  __shared__ unsigned int s_nan;
+  const int wid = threadIdx.x >> 5;
+  const int row = blockIdx.x * 8 + wid;
   const uint32_t lane = lane_id();
-  if (row >= batch) return;
+  const bool row_ok = row < batch;
+  if (threadIdx.x == 0) s_nan = 0;
   float acc[NCLS];
 #pragma unroll
   for (int c = 0; c < NCLS; ++c) acc[c] = 0.0f;
-  const __nv_bfloat16* hr = h + static_cast<size_t>(row) * hidden;
-  for (int k = lane; k < hidden; k += 32) {
-    const float hv = __bfloat162float(hr[k]);
-    const float2* wk = reinterpret_cast<const float2*>(w + static_cast<size_t>(k) * NCLS);  // 40-byte rows: 8-byte aligned
+  const __nv_bfloat16* hr = h + static_cast<size_t>(row_ok ? row : 0) * hidden;
+  for (int k0 = 0; k0 < hidden; k0 += HF_CHUNK) {
+    const int kc = min(HF_CHUNK, hidden - k0);
+    __syncthreads();
+    {  // stage the chunk with 16-byte loads, several in flight per thread (a serial 4-byte loop here cost 20 us)
+      const float4* w4 = reinterpret_cast<const float4*>(w + static_cast<size_t>(k0) * NCLS);
+      const int n4 = (kc * NCLS) >> 2;
+#pragma unroll 5
+      for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+        const float4 v = w4[i];
+        const float e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-    for (int c2 = 0; c2 < NCLS / 2; ++c2) {
-      const float2 ww = wk[c2];
-      acc[2 * c2] = fmaf(hv, ww.x, acc[2 * c2]);
-      acc[2 * c2 + 1] = fmaf(hv, ww.y, acc[2 * c2 + 1]);
+        for (int t = 0; t < 4; ++t) {
+          const int idx = 4 * i + t;
+          s_w[(idx / NCLS) * HF_PITCH + idx % NCLS] = e[t];
+        }
+      }
+      for (int idx = (n4 << 2) + threadIdx.x; idx < kc * NCLS; idx += blockDim.x)
+        s_w[(idx / NCLS) * HF_PITCH + idx % NCLS] = w[static_cast<size_t>(k0) * NCLS + idx];
+    }
+    __syncthreads();
+    if (row_ok) {
+#pragma unroll 8
+      for (int k = lane; k < kc; k += 32) {
+        const float hv = __bfloat162float(hr[k0 + k]);
+        const float* wk = s_w + k * HF_PITCH;
+#pragma unroll
+        for (int c = 0; c < NCLS; ++c) acc[c] = fmaf(hv, wk[c], acc[c]);
+      }
     }
   }
 #pragma unroll
   for (int c = 0; c < NCLS; ++c) acc[c] = warp_sum(acc[c]) + bias[c];
-  if (lane != 0) return;
 
-  float mx = acc[0];
+  float my_loss = 0.0f, my_corr = 0.0f;
+  if (row_ok && lane == 0) {
+    float mx = acc[0];
 #pragma unroll
-  for (int c = 1; c < NCLS; ++c) mx = fmaxf(mx, acc[c]);
-  float e[NCLS], sum = 0.0f;
+    for (int c = 1; c < NCLS; ++c) mx = fmaxf(mx, acc[c]);
+    float e[NCLS], sum = 0.0f;
 #pragma unroll
-  for (int c = 0; c < NCLS; ++c) { e[c] = __expf(acc[c] - mx); sum += e[c]; }
-  const float inv = 1.0f / sum;
-  if (logits_out) {
+    for (int c = 0; c < NCLS; ++c) { e[c] = __expf(acc[c] - mx); sum += e[c]; }
+    const float inv = 1.0f / sum;
+    if (logits_out) {
 #pragma unroll
-    for (int c = 0; c < NCLS; ++c) logits_out[static_cast<size_t>(row) * NCLS + c] = acc[c];
+      for (int c = 0; c < NCLS; ++c) logits_out[static_cast<size_t>(row) * NCLS + c] = acc[c];
+    }
+    if (probs_out) {
+#pragma unroll
+      for (int c = 0; c < NCLS; ++c) probs_out[static_cast<size_t>(row) * NCLS + c] = e[c] * inv;
+    }
+    if (labels) {
+      const int y = labels[row];
+      float target = 0.0f;
+      int greater = 0;
+#pragma unroll
+      for (int c = 0; c < NCLS; ++c) if (c == y) target = acc[c];
+#pragma unroll
+      for (int c = 0; c < NCLS; ++c) greater += (acc[c] > target) ? 1 : 0;
+      const float loss = (mx - target) + __logf(sum);
+      if (dlogits) {
+#pragma unroll
+        for (int c = 0; c < NCLS; ++c)
+          dlogits[static_cast<size_t>(row) * NCLS + c] = (e[c] * inv - (c == y ? 1.0f : 0.0f)) * grad_scale;
+      }
+      my_loss = loss * loss_scale;
+      my_corr = greater == 0 ? loss_scale : 0.0f;
+      if (!(fabsf(loss) <= 3.0e38f)) atomicOr(&s_nan, 1u);  // catches NaN and Inf
+    }
   }
-  if (probs_out) {
+  if (lane == 0) { s_loss[wid] = my_loss; s_corr[wid] = my_corr; }
+  __syncthreads();
+  if (threadIdx.x == 0 && state && labels) {   // one atomic per CTA instead of one per example
+    float l = 0.0f, cnt = 0.0f;
 #pragma unroll
-    for (int c = 0; c < NCLS; ++c) probs_out[static_cast<size_t>(row) * NCLS + c] = e[c] * inv;
-  }
-  if (!labels) return;
-  const int y = labels[row];
-  float target = 0.0f;
-  int greater = 0;
-#pragma unroll
-  for (int c = 0; c < NCLS; ++c) if (c == y) target = acc[c];
-#pragma unroll
-  for (int c = 0; c < NCLS; ++c) greater += (acc[c] > target) ? 1 : 0;
-  const float loss = (mx - target) + __logf(sum);
-  if (dlogits) {
-#pragma unroll
-    for (int c = 0; c < NCLS; ++c)
-      dlogits[static_cast<size_t>(row) * NCLS + c] = (e[c] * inv - (c == y ? 1.0f : 0.0f)) * grad_scale;
-  }
-  if (state) {
-    atomicAdd(&state->loss_sum, loss * loss_scale);
-    if (greater == 0) atomicAdd(&state->correct, loss_scale);
-    if (!(fabsf(loss) <= 3.0e38f)) atomicOr(&state->nan_flag, 1u);  // catches NaN and Inf
+    for (int i = 0; i < 8; ++i) { l += s_loss[i]; cnt += s_corr[i]; }
+    atomicAdd(&state->loss_sum, l);
+    if (cnt != 0.0f) atomicAdd(&state->correct, cnt);
+    if (s_nan) atomicOr(&state->nan_flag, 1u);
   }
 }
 

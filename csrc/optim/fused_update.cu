@@ -12,17 +12,19 @@ namespace dtm {
 __global__ void __launch_bounds__(256)
 fused_update_kernel(const dtm_update_config cfg, dtm_train_state* __restrict__ st, float* __restrict__ w,
                     float* __restrict__ grad, float* __restrict__ slot0, float* __restrict__ slot1,
-                    float* __restrict__ ema, __nv_bfloat16* __restrict__ w_bf16, float grad_scale) {
+                    float* __restrict__ ema, __nv_bfloat16* __restrict__ w_bf16, float grad_scale, int lo, int hi,
+                    int do_finish) {
   const UpdateScalars u = make_update_scalars(cfg, st, grad_scale);
-  const int n4 = cfg.total >> 2;
+  const int lo4 = lo >> 2, n4 = hi >> 2;
   __shared__ float s_wl[DTM_MAX_SEGMENTS];
   if (threadIdx.x < DTM_MAX_SEGMENTS) s_wl[threadIdx.x] = 0.0f;
   __syncthreads();
   int cur_seg = -1;
   float cur_sq = 0.0f;
-  for (int i4 = blockIdx.x * blockDim.x + threadIdx.x; i4 < n4; i4 += gridDim.x * blockDim.x) {
+  int seg = 0;
+  for (int i4 = lo4 + blockIdx.x * blockDim.x + threadIdx.x; i4 < n4; i4 += gridDim.x * blockDim.x) {
     const int i = i4 << 2;
-    const int seg = segment_of(cfg, i);         // segment offsets are multiples of 64: a float4 never straddles
+    seg = segment_advance(cfg, seg, i);         // segment offsets are multiples of 64: a float4 never straddles
     const float wd = cfg.seg_wd[seg];
     const float4 wv = *reinterpret_cast<const float4*>(w + i);
     const float4 gv = *reinterpret_cast<const float4*>(grad + i);
@@ -34,14 +36,11 @@ fused_update_kernel(const dtm_update_config cfg, dtm_train_state* __restrict__ s
       }
       cur_sq += wv.x * wv.x + wv.y * wv.y + wv.z * wv.z + wv.w * wv.w;
     }
-    float o[4];
-    o[0] = update_element(cfg, u, wv.x, gv.x, wd, slot0, slot1, ema, i + 0);
-    o[1] = update_element(cfg, u, wv.y, gv.y, wd, slot0, slot1, ema, i + 1);
-    o[2] = update_element(cfg, u, wv.z, gv.z, wd, slot0, slot1, ema, i + 2);
-    o[3] = update_element(cfg, u, wv.w, gv.w, wd, slot0, slot1, ema, i + 3);
-    *reinterpret_cast<float4*>(w + i) = make_float4(o[0], o[1], o[2], o[3]);
+    const float4 o = update_vec4(cfg, u, wv, gv, wd, slot0, slot1, ema, i);
+    *reinterpret_cast<float4*>(w + i) = o;
     if (cfg.seg_zero_grad[seg]) *reinterpret_cast<float4*>(grad + i) = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (w_bf16) *reinterpret_cast<uint2*>(w_bf16 + i) = make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
+    if (w_bf16) *reinterpret_cast<uint2*>(w_bf16 + i) = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+    if (seg == cfg.pack_seg) pack_conv2_vec4(cfg, i - cfg.seg_offset[seg], o);
   }
   if (cur_seg >= 0) atomicAdd(&s_wl[cur_seg], cur_sq);
   __syncthreads();
@@ -54,8 +53,10 @@ fused_update_kernel(const dtm_update_config cfg, dtm_train_state* __restrict__ s
   __syncthreads();
   if (s_last && threadIdx.x == 0) {
     __threadfence();
-    const float lr_plain = cfg.base_lr * powf(cfg.decay_rate, cfg.decay_steps > 0 ? floorf((float)(st->global_step / cfg.decay_steps)) : 0.f);
-    finish_step(cfg, st, lr_plain);
+    if (do_finish) {
+      const float lr_plain = cfg.base_lr * powf(cfg.decay_rate, cfg.decay_steps > 0 ? floorf((float)(st->global_step / cfg.decay_steps)) : 0.f);
+      finish_step(cfg, st, lr_plain);
+    }
     st->ticket = 0;
   }
 }
@@ -73,23 +74,34 @@ __global__ void state_init_kernel(dtm_train_state* st, long long step, float b1,
 
 }  // namespace dtm
 
-extern "C" int dtm_fused_update(const dtm_update_config* cfg, dtm_train_state* state, float* w, float* grad, float* slot0,
-                                float* slot1, float* ema, void* w_bf16, float grad_scale, void* stream) {
+extern "C" int dtm_fused_update_range(const dtm_update_config* cfg, dtm_train_state* state, float* w, float* grad, float* slot0,
+                                      float* slot1, float* ema, void* w_bf16, float grad_scale, int lo, int hi, int do_finish,
+                                      int max_ctas, void* stream) {
   using namespace dtm;
   if (!cfg || !state || !w || !grad) return dtm_fail("fused_update: null argument");
   if (cfg->n_segments < 1 || cfg->n_segments > DTM_MAX_SEGMENTS) return dtm_fail("fused_update: bad segment count");
   if (cfg->total % 64 != 0) return dtm_fail("fused_update: total must be a multiple of 64");
   for (int s = 0; s <= cfg->n_segments; ++s)
     if (cfg->seg_offset[s] % 64 != 0) return dtm_fail("fused_update: segment offsets must be multiples of 64");
+  if (lo < 0 || hi > cfg->total || lo >= hi || lo % 64 || hi % 64) return dtm_fail("fused_update: bad element range");
   if (cfg->optimizer == DTM_OPT_ADAM && (!slot0 || !slot1)) return dtm_fail("fused_update: Adam needs both slots");
   if (cfg->optimizer == DTM_OPT_MOMENTUM && !slot0) return dtm_fail("fused_update: Momentum needs slot0");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const int n4 = cfg->total / 4;
-  const int grid = min((n4 + 255) / 256, 8 * device_sm_count());
+  const int n4 = (hi - lo) / 4;
+  int grid = min((n4 + 255) / 256, 8 * device_sm_count());
+  if (max_ctas > 0) grid = min(grid, max_ctas);
+  if (cfg->pack_seg >= cfg->n_segments || (cfg->pack_seg >= 0 && (!cfg->pack_fwd || !cfg->pack_dgrad)))
+    return dtm_fail("fused_update: pack_seg set without both pack buffers");
   fused_update_kernel<<<grid, 256, 0, s>>>(*cfg, state, w, grad, slot0, slot1, ema, static_cast<__nv_bfloat16*>(w_bf16),
-                                           grad_scale);
+                                           grad_scale, lo, hi, do_finish);
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
+}
+
+extern "C" int dtm_fused_update(const dtm_update_config* cfg, dtm_train_state* state, float* w, float* grad, float* slot0,
+                                float* slot1, float* ema, void* w_bf16, float grad_scale, void* stream) {
+  if (!cfg) return dtm::dtm_fail("fused_update: null argument");
+  return dtm_fused_update_range(cfg, state, w, grad, slot0, slot1, ema, w_bf16, grad_scale, 0, cfg->total, 1, 0, stream);
 }
 
 extern "C" int dtm_state_init(dtm_train_state* state, long long global_step, float beta1, float beta2, void* stream) {

@@ -33,6 +33,14 @@ __device__ __forceinline__ UpdateScalars make_update_scalars(const dtm_update_co
   return u;
 }
 
+// Grid-stride loops visit increasing indices, so the segment only ever moves forward: amortised O(1) instead of a
+// scan per element.
+__device__ __forceinline__ int segment_advance(const dtm_update_config& cfg, int seg, int i) {
+#pragma unroll 1
+  while (seg + 1 < cfg.n_segments && i >= cfg.seg_offset[seg + 1]) ++seg;
+  return seg;
+}
+
 __device__ __forceinline__ int segment_of(const dtm_update_config& cfg, int i) {
   int s = 0;
 #pragma unroll 1
@@ -63,6 +71,69 @@ __device__ __forceinline__ float update_element(const dtm_update_config& cfg, co
     ema[i] = s - (1.0f - u.ema_keep) * (s - w_new);
   }
   return w_new;
+}
+
+// Four consecutive elements at once: every state array is touched with one 16-byte load and one 16-byte store.
+__device__ __forceinline__ float4 update_vec4(const dtm_update_config& cfg, const UpdateScalars& u, float4 w, float4 gs, float wd,
+                                              float* __restrict__ slot0, float* __restrict__ slot1, float* __restrict__ ema, int i) {
+  float wv[4] = {w.x, w.y, w.z, w.w};
+  float g[4] = {gs.x * u.grad_scale + wd * w.x, gs.y * u.grad_scale + wd * w.y, gs.z * u.grad_scale + wd * w.z,
+                gs.w * u.grad_scale + wd * w.w};
+  float o[4];
+  if (cfg.optimizer == DTM_OPT_ADAM) {
+    const float4 m4 = *reinterpret_cast<const float4*>(slot0 + i);
+    const float4 v4 = *reinterpret_cast<const float4*>(slot1 + i);
+    float m[4] = {m4.x, m4.y, m4.z, m4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      m[k] = cfg.beta1 * m[k] + (1.0f - cfg.beta1) * g[k];
+      v[k] = cfg.beta2 * v[k] + (1.0f - cfg.beta2) * g[k] * g[k];
+      // sqrt via one MUFU.RSQ (v * rsqrt(v)) and an approximate divide: ~1e-7 relative error, a fifth of the
+      // instructions of the IEEE sequences - this kernel was issue-bound, not memory-bound, with them
+      const float sq = v[k] > 0.0f ? v[k] * rsqrtf(v[k]) : 0.0f;
+      o[k] = wv[k] - u.lr * __fdividef(m[k], sq + cfg.epsilon);
+    }
+    *reinterpret_cast<float4*>(slot0 + i) = make_float4(m[0], m[1], m[2], m[3]);
+    *reinterpret_cast<float4*>(slot1 + i) = make_float4(v[0], v[1], v[2], v[3]);
+  } else if (cfg.optimizer == DTM_OPT_MOMENTUM) {
+    const float4 a4 = *reinterpret_cast<const float4*>(slot0 + i);
+    float a[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      a[k] = cfg.momentum * a[k] + g[k];
+      o[k] = wv[k] - u.lr * a[k];
+    }
+    *reinterpret_cast<float4*>(slot0 + i) = make_float4(a[0], a[1], a[2], a[3]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o[k] = wv[k] - u.lr * g[k];
+  }
+  if (ema) {
+    const float4 s4 = *reinterpret_cast<const float4*>(ema + i);
+    const float k1 = 1.0f - u.ema_keep;
+    *reinterpret_cast<float4*>(ema + i) = make_float4(s4.x - k1 * (s4.x - o[0]), s4.y - k1 * (s4.y - o[1]), s4.z - k1 * (s4.z - o[2]),
+                                                      s4.w - k1 * (s4.w - o[3]));
+  }
+  return make_float4(o[0], o[1], o[2], o[3]);
+}
+
+// Emits the conv2 operand images for 4 consecutive filter elements starting at flat index `rel` inside the conv2
+// segment ((tap*32 + ci)*64 + co, co % 4 == 0).  Same mapping as csrc/conv/conv2_pack.cu.
+__device__ __forceinline__ void pack_conv2_vec4(const dtm_update_config& cfg, int rel, float4 o) {
+  const int co = rel & 63, ci = (rel >> 6) & 31, tap = rel >> 11;
+  if (tap >= 25) return;
+  __nv_bfloat16* fwd = static_cast<__nv_bfloat16*>(cfg.pack_fwd);
+  __nv_bfloat16* dg = static_cast<__nv_bfloat16*>(cfg.pack_dgrad);
+  const int k = tap * 32 + ci;
+  const float v[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+  for (int t = 0; t < 4; ++t) fwd[((k >> 3) * 64 + co + t) * 8 + (k & 7)] = __float2bfloat16(v[t]);
+  const int kd = (24 - tap) * 64 + co;          // co..co+3 stay inside one group of 8
+  uint2 pk;
+  __nv_bfloat162 lo2 = __floats2bfloat162_rn(o.x, o.y), hi2 = __floats2bfloat162_rn(o.z, o.w);
+  pk.x = *reinterpret_cast<uint32_t*>(&lo2);
+  pk.y = *reinterpret_cast<uint32_t*>(&hi2);
+  *reinterpret_cast<uint2*>(dg + ((kd >> 3) * 32 + ci) * 8 + (kd & 7)) = pk;
 }
 
 // End-of-step bookkeeping, executed by exactly one thread after every element has been updated:

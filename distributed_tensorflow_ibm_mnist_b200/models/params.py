@@ -121,4 +121,5 @@ class FlatParams:
             cfg.seg_wd[i] = float(v.wd or 0.0)
             cfg.seg_zero_grad[i] = 1 if v.atomic_grad else 0
         cfg.seg_offset[len(self.spec.variables)] = self.total
+        cfg.pack_seg = -1
         return cfg

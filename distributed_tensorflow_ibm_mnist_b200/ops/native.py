@@ -20,14 +20,16 @@ MAX_SEGMENTS = 16
 P, I, F = c_void_p, c_int, c_float
 _lib.register("dtm_conv1_fwd", [P, I, I, P, P, I, I, P, P, P, P])
 _lib.register("dtm_conv1_wgrad", [P, I, I, P, P, I, P, P, P])
-_lib.register("dtm_conv2_fwd", [P, P, P, I, I, P, P, P, P])
-_lib.register("dtm_conv2_dgrad", [P, P, P, P, I, I, P, P])
+_lib.register("dtm_conv2_fwd", [P, P, P, P, I, I, P, P, P, P])
+_lib.register("dtm_conv2_dgrad", [P, P, P, P, P, I, I, P, P])
+_lib.register("dtm_conv2_pack_weights", [P, P, P, P])
 _lib.register("dtm_conv2_wgrad", [P, P, I, P, P])
 _lib.register("dtm_unpool2", [P, P, P, I, I, P, P, P])
 _lib.register("dtm_colsum_bf16", [P, I, I, P, P])
 _lib.register("dtm_head_forward", [P, I, I, P, P, P, F, F, P, P, P, P, P])
 _lib.register("dtm_head_backward", [P, I, I, P, P, F, P, P, P, P, P])
 _lib.register("dtm_fused_update", [P, P, P, P, P, P, P, P, F, P])
+_lib.register("dtm_fused_update_range", [P, P, P, P, P, P, P, P, F, I, I, I, I, P])
 _lib.register("dtm_state_init", [P, c_longlong, F, F, P])
 _lib.register("dtm_tensor_stats_scratch_bytes", [ctypes.c_size_t], ctypes.c_size_t)
 _lib.register("dtm_tensor_stats", [P, ctypes.c_size_t, I, P, P, ctypes.c_size_t, P])
@@ -60,6 +62,7 @@ class UpdateConfig(ctypes.Structure):
         ("seg_offset", c_int * (MAX_SEGMENTS + 1)),
         ("seg_wd", c_float * MAX_SEGMENTS),
         ("seg_zero_grad", c_int * MAX_SEGMENTS),
+        ("pack_seg", c_int), ("reserved2", c_int), ("pack_fwd", c_void_p), ("pack_dgrad", c_void_p),
     ]
 
 
@@ -90,14 +93,19 @@ def conv1_wgrad(x, grad_pooled, argmax, dw, db, *, channels=1):
                                ptr(dw), ptr(db), current_stream()), "conv1_wgrad")
 
 
-def conv2_fwd(p1_planes, w2_bf16, bias, p2, argmax, act2=None, *, batch, lrn=False):
-    check(_L().dtm_conv2_fwd(ptr(p1_planes), ptr(w2_bf16), ptr(bias), batch, int(lrn), ptr(p2), ptr(argmax), ptr(act2),
-                             current_stream()), "conv2_fwd")
+def conv2_fwd(p1_planes, w2_bf16, bias, p2, argmax, act2=None, *, batch, lrn=False, packed=None):
+    check(_L().dtm_conv2_fwd(ptr(p1_planes), ptr(w2_bf16), ptr(packed), ptr(bias), batch, int(lrn), ptr(p2), ptr(argmax),
+                             ptr(act2), current_stream()), "conv2_fwd")
 
 
-def conv2_dgrad(dz2_planes, w2_bf16, p1_planes, pool_raw, dpool1, *, batch, lrn=False):
-    check(_L().dtm_conv2_dgrad(ptr(dz2_planes), ptr(w2_bf16), ptr(p1_planes), ptr(pool_raw), batch, int(lrn), ptr(dpool1),
-                               current_stream()), "conv2_dgrad")
+def conv2_pack_weights(w2_bf16, packed_fwd, packed_dgrad):
+    """Re-pack the bf16 conv2 filter into the two 102400-byte operand images (see include/dtm_b200.h)."""
+    check(_L().dtm_conv2_pack_weights(ptr(w2_bf16), ptr(packed_fwd), ptr(packed_dgrad), current_stream()), "conv2_pack_weights")
+
+
+def conv2_dgrad(dz2_planes, w2_bf16, p1_planes, pool_raw, dpool1, *, batch, lrn=False, packed=None):
+    check(_L().dtm_conv2_dgrad(ptr(dz2_planes), ptr(w2_bf16), ptr(packed), ptr(p1_planes), ptr(pool_raw), batch, int(lrn),
+                               ptr(dpool1), current_stream()), "conv2_dgrad")
 
 
 def conv2_wgrad(p1_planes, dz2_planes, dw2, *, batch):
@@ -129,6 +137,14 @@ def head_backward(h, w, dlogits, dh, dw, db_out, db_hidden, *, inv_keep=1.0):
 def fused_update(cfg: UpdateConfig, state, w, grad, slot0, slot1, ema, w_bf16, *, grad_scale=1.0):
     check(_L().dtm_fused_update(ctypes.byref(cfg), ptr(state), ptr(w), ptr(grad), ptr(slot0), ptr(slot1), ptr(ema), ptr(w_bf16),
                                 float(grad_scale), current_stream()), "fused_update")
+
+
+def fused_update_range(cfg: UpdateConfig, state, w, grad, slot0, slot1, ema, w_bf16, lo, hi, *, grad_scale=1.0, finish=True,
+                       max_ctas=0):
+    check(_L().dtm_fused_update_range(ctypes.byref(cfg), ptr(state), ptr(w), ptr(grad), ptr(slot0), ptr(slot1), ptr(ema),
+                                      ptr(w_bf16), float(grad_scale), int(lo), int(hi), int(finish), int(max_ctas),
+                                      current_stream()),
+          "fused_update_range")
 
 
 def state_init(state, global_step=0, beta1=0.9, beta2=0.999):

@@ -45,16 +45,27 @@ class NativeEngine:
         self.eval_state = native.new_state(self.device)
         native.state_init(self.eval_state)
         self._alloc_activations(keep_logits)
+        # the update kernels keep the conv2 operand images in step with the weights (dtm_update_config.pack_*)
+        self.cfg.pack_seg = self.flat.index["conv2/weights"]
+        self.cfg.pack_fwd = self.w2_fwd.data_ptr()
+        self.cfg.pack_dgrad = self.w2_dgrad.data_ptr()
         self._graphs: dict[int, torch.cuda.CUDAGraph] = {}
         self._side = torch.cuda.Stream(device=self.device)
         self._comm_stream = torch.cuda.Stream(device=self.device)
-        self._fork_ev = [torch.cuda.Event() for _ in range(6)]
+        self._fork_ev = [torch.cuda.Event() for _ in range(10)]
         # gradient buckets in flat-buffer order: the fc/head variables (93 % of the bytes, ready right after the first
         # backward GEMMs) and the conv variables (ready last).  With >1 rank bucket 0 is reduced + updated on its own
         # stream while the conv backward still runs.
         split = self.flat.offsets["local3/weights"]
         self.buckets = [(split, self.flat.total), (0, split)]
         self.launches_per_step = 0
+        # experiment switches (tools/ablate.py): kernels to leave out of the step (timing only - results are then wrong) and a
+        # flag that puts every kernel on the main stream
+        import os as _os
+        self._skip = set(filter(None, _os.environ.get("DTM_SKIP", "").split(",")))
+        self._serial = _os.environ.get("DTM_SERIAL", "0") == "1"
+        self._early_update_ctas = int(_os.environ.get("DTM_EARLY_UPDATE_CTAS", "0"))
+        self.trace = None   # set to a list to collect (label, cuda event) marks on the main stream (tools/phase_times.py)
 
     # ------------------------------------------------------------------------------------------------
     def _alloc_activations(self, keep_logits: bool) -> None:
@@ -79,6 +90,8 @@ class NativeEngine:
         self.dp2 = z(B, 3136, dtype=torch.bfloat16)
         self.dz2 = layouts.alloc_planes(B, 64, dev)
         self.dpool1 = z(B, 196, 32, dtype=torch.bfloat16)
+        self.w2_fwd = z(25 * 32 * 64, dtype=torch.bfloat16)      # conv2 filter, packed as tcgen05 operand images
+        self.w2_dgrad = z(25 * 32 * 64, dtype=torch.bfloat16)
 
     # ---- parameters / state ---------------------------------------------------------------------------
     def load_params(self, tensors, *, ema=None, slots=None, global_step=0, loss_avg=None) -> None:
@@ -89,6 +102,7 @@ class NativeEngine:
             for k, d in enumerate(slots):
                 if d:
                     self.flat.load_slot_dict(k, d)
+        native.conv2_pack_weights(self.flat.weight_bf16("conv2/weights"), self.w2_fwd, self.w2_dgrad)
         native.state_init(self.state, global_step, self.cfg.beta1, self.cfg.beta2)
         if loss_avg:
             st = native.read_state(self.state)
@@ -127,26 +141,48 @@ class NativeEngine:
     def state_ptr_step(self) -> int:
         return self.state.data_ptr()  # global_step is the first field of dtm_train_state
 
+    def _on(self, name: str) -> bool:
+        return name not in self._skip
+
+    def _stream(self, st):
+        """Side stream, or the current one when the serial experiment switch is set."""
+        return torch.cuda.current_stream() if self._serial else st
+
+    def _mark(self, label: str) -> None:
+        if self.trace is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(torch.cuda.current_stream())
+            self.trace.append((label, ev))
+
     # ---- the kernel sequence ----------------------------------------------------------------------------
     def _forward(self, x, labels, *, training: bool, state, count=None) -> None:
         s, f, B = self.spec, self.flat, self.B
         n = 0
-        native.conv1_fwd(x, f.weight("conv1/weights"), f.weight("conv1/biases"), self.p1, self.arg1, self.pool_raw,
-                         channels=s.channels, lrn=s.lrn); n += 1
-        native.conv2_fwd(self.p1, f.weight_bf16("conv2/weights"), f.weight("conv2/biases"), self.p2, self.arg2, self.act2,
-                         batch=B, lrn=s.lrn); n += 1
+        self._mark("start")
+        if self._on("conv1_fwd"):
+            native.conv1_fwd(x, f.weight("conv1/weights"), f.weight("conv1/biases"), self.p1, self.arg1, self.pool_raw,
+                             channels=s.channels, lrn=s.lrn); n += 1
+        self._mark("conv1_fwd")
+        if self._on("conv2_fwd"):
+            native.conv2_fwd(self.p1, f.weight_bf16("conv2/weights"), f.weight("conv2/biases"), self.p2, self.arg2, self.act2,
+                             batch=B, lrn=s.lrn, packed=self.w2_fwd); n += 1
+        self._mark("conv2_fwd")
         drop_here = training and s.keep_prob < 1.0 and not s.fc2
-        native.gemm_bf16(self.p2, 0, f.weight_bf16("local3/weights"), 1, self.h1, B, s.fc1, 3136,
-                         epilogue=native.EPI_BIAS_RELU_BF16, bias=f.weight("local3/biases"),
-                         keep_prob=s.keep_prob if drop_here else 1.0, seed=self.seed, step_ptr=self.state_ptr_step); n += 1
+        if self._on("fc1_fwd"):
+            native.gemm_bf16(self.p2, 0, f.weight_bf16("local3/weights"), 1, self.h1, B, s.fc1, 3136,
+                             epilogue=native.EPI_BIAS_RELU_BF16, bias=f.weight("local3/biases"),
+                             keep_prob=s.keep_prob if drop_here else 1.0, seed=self.seed, step_ptr=self.state_ptr_step); n += 1
+        self._mark("fc1_fwd")
         h = self.h1
         if s.fc2:
             native.gemm_bf16(self.h1, 0, f.weight_bf16("local4/weights"), 1, self.h2, B, s.fc2, s.fc1,
                              epilogue=native.EPI_BIAS_RELU_BF16, bias=f.weight("local4/biases")); n += 1
             h = self.h2
-        native.head_forward(h, f.weight("softmax_linear/weights"), f.weight("softmax_linear/biases"), labels,
-                            grad_scale=1.0 / B, loss_scale=1.0 / B, logits=self.logits, probs=self.probs,
-                            dlogits=self.dlogits if training else None, state=state); n += 1
+        if self._on("head_fwd"):
+            native.head_forward(h, f.weight("softmax_linear/weights"), f.weight("softmax_linear/biases"), labels,
+                                grad_scale=1.0 / B, loss_scale=1.0 / B, logits=self.logits, probs=self.probs,
+                                dlogits=self.dlogits if training else None, state=state); n += 1
+        self._mark("head_fwd")
         if count is not None:
             count[0] += n
 
@@ -155,9 +191,11 @@ class NativeEngine:
         n = 0
         h = self.h2 if s.fc2 else self.h1
         inv_keep = 1.0 / s.keep_prob if (s.keep_prob < 1.0 and not s.fc2) else 1.0
-        native.head_backward(h, f.weight("softmax_linear/weights"), self.dlogits, self.dh_last,
-                             f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
-                             f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep); n += 1
+        if self._on("head_bwd"):
+            native.head_backward(h, f.weight("softmax_linear/weights"), self.dlogits, self.dh_last,
+                                 f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
+                                 f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep); n += 1
+        self._mark("head_bwd")
         if s.fc2:
             # dW4 = h1^T . dY2 ; dY1 = (dY2 . W4^T) * [h1 > 0] ; db3 = colsum(dY1)
             native.gemm_bf16(self.h1, 1, self.dh_last, 1, f.gradient("local4/weights"), s.fc1, s.fc2, B); n += 1
@@ -168,48 +206,73 @@ class NativeEngine:
         else:
             dy1 = self.dh_last
         main = torch.cuda.current_stream()
+        lo0, hi0 = self.buckets[0]
         # fork: the two big fc GEMMs are independent
         self._fork_ev[0].record(main)
         self._side.wait_event(self._fork_ev[0])
-        with torch.cuda.stream(self._side):
-            native.gemm_bf16(self.p2, 1, dy1, 1, f.gradient("local3/weights"), 3136, s.fc1, B); n += 1
+        with torch.cuda.stream(self._stream(self._side)):
+            if self._on("dW3"):
+                native.gemm_bf16(self.p2, 1, dy1, 1, f.gradient("local3/weights"), 3136, s.fc1, B); n += 1
             self._fork_ev[1].record(self._side)
-        native.gemm_bf16(dy1, 0, f.weight_bf16("local3/weights"), 0, self.dp2, B, 3136, s.fc1,
-                         epilogue=native.EPI_MASK_BF16, ref=self.p2); n += 1
-        overlap_comm = self.sharded and with_comm
-        if overlap_comm:
-            # bucket 0 (fc + head variables): all gradients are complete once the dW GEMM is done, and the last reader of
-            # the fc weights (the dP2 GEMM above) has been issued: reduce + update them now, beside the conv backward.
+        if self._on("dP2"):
+            native.gemm_bf16(dy1, 0, f.weight_bf16("local3/weights"), 0, self.dp2, B, 3136, s.fc1,
+                             epilogue=native.EPI_MASK_BF16, ref=self.p2); n += 1
+        self._mark("dP2_gemm")
+        # bucket 0 (fc + head variables, 98 % of the elements): every gradient is complete once the dW GEMM is done and the
+        # last reader of the fc weights (the dP2 GEMM above) has finished -> update it now, on its own stream, beside the
+        # conv backward (tensor-core / latency bound kernels that leave the memory system idle).
+        early_update = with_comm and self._on("early_update")
+        if early_update:
             self._fork_ev[4].record(main)
             self._comm_stream.wait_event(self._fork_ev[4])
             self._comm_stream.wait_event(self._fork_ev[1])
-            with torch.cuda.stream(self._comm_stream):
-                lo, hi = self.buckets[0]
-                self.comm.fused_allreduce_update(self.cfg, self.state, f, lo, hi, finish=False, overlapped=True); n += 1
+            with torch.cuda.stream(self._stream(self._comm_stream)):
+                if self.sharded:
+                    self.comm.fused_allreduce_update(self.cfg, self.state, f, lo0, hi0, finish=False, overlapped=True)
+                elif self._on("update0"):
+                    # capped grid: the kernel trickles along in the background instead of occupying every SM slot and
+                    # stalling the conv kernels queued behind it
+                    native.fused_update_range(self.cfg, self.state, f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, lo0, hi0,
+                                              finish=False, max_ctas=self._early_update_ctas)
+                n += 1
                 self._fork_ev[5].record(self._comm_stream)
-        native.unpool2(self.dp2, self.arg2, self.act2, self.dz2, f.gradient("conv2/biases"), batch=B, lrn=s.lrn); n += 1
-        # fork: conv2 wgrad runs beside dgrad -> conv1 wgrad
+        if self._on("unpool2"):
+            native.unpool2(self.dp2, self.arg2, self.act2, self.dz2, f.gradient("conv2/biases"), batch=B, lrn=s.lrn); n += 1
+        self._mark("unpool2")
+        # dgrad first: it and wgrad both need > 113 KB of shared memory and cannot share an SM, so launching them together
+        # only serialises them.  conv1_wgrad (26 KB, CUDA cores) does co-reside with the tensor-core wgrad.
+        if self._on("conv2_dgrad"):
+            native.conv2_dgrad(self.dz2, f.weight_bf16("conv2/weights"), self.p1, self.pool_raw, self.dpool1, batch=B, lrn=s.lrn,
+                               packed=self.w2_dgrad); n += 1
+        self._mark("conv2_dgrad")
         self._fork_ev[2].record(main)
         self._side.wait_event(self._fork_ev[2])
-        with torch.cuda.stream(self._side):
-            native.conv2_wgrad(self.p1, self.dz2, f.gradient("conv2/weights"), batch=B); n += 1
+        with torch.cuda.stream(self._stream(self._side)):
+            if self._on("conv2_wgrad"):
+                native.conv2_wgrad(self.p1, self.dz2, f.gradient("conv2/weights"), batch=B); n += 1
             self._fork_ev[3].record(self._side)
-        native.conv2_dgrad(self.dz2, f.weight_bf16("conv2/weights"), self.p1, self.pool_raw, self.dpool1, batch=B, lrn=s.lrn); n += 1
-        native.conv1_wgrad(x, self.dpool1, self.arg1, f.gradient("conv1/weights"), f.gradient("conv1/biases"),
-                           channels=s.channels); n += 1
+        if self._on("conv1_wgrad"):
+            native.conv1_wgrad(x, self.dpool1, self.arg1, f.gradient("conv1/weights"), f.gradient("conv1/biases"),
+                               channels=s.channels); n += 1
+        self._mark("conv1_wgrad")
         main.wait_event(self._fork_ev[1])
         main.wait_event(self._fork_ev[3])
-        if overlap_comm:
+        self._mark("join_wgrad")
+        if early_update:
             main.wait_event(self._fork_ev[5])
+        self._mark("join_update0")
+        self._early_update_done = early_update
         count[0] += n
 
     def _update(self, count) -> None:
+        """Close the step: the conv bucket (bucket 0 was launched from inside the backward pass)."""
         f = self.flat
+        lo, hi = self.buckets[1] if getattr(self, "_early_update_done", False) else (0, f.total)
         if self.sharded:
-            lo, hi = self.buckets[1]      # conv variables; bucket 0 was launched from inside the backward pass
             self.comm.fused_allreduce_update(self.cfg, self.state, f, lo, hi, finish=True)
         else:
-            native.fused_update(self.cfg, self.state, f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, grad_scale=1.0)
+            native.fused_update_range(self.cfg, self.state, f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, lo, hi, finish=True)
+        self._mark("update_tail")
         count[0] += 1
 
     def _step_body(self, slot: int) -> int:
@@ -252,12 +315,12 @@ class NativeEngine:
 
     def _snapshot(self):
         f = self.flat
-        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state]
+        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state, self.w2_fwd, self.w2_dgrad]
         return [b.clone() if b is not None else None for b in bufs]
 
     def _restore(self, snap) -> None:
         f = self.flat
-        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state]
+        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state, self.w2_fwd, self.w2_dgrad]
         for b, s in zip(bufs, snap):
             if b is not None:
                 b.copy_(s)

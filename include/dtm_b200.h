@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define DTM_ABI_VERSION 1
+#define DTM_ABI_VERSION 3
 
 /* GEMM epilogues */
 #define DTM_EPI_STORE_F32 0      /* D(fp32)  = alpha * acc          (split-K: red.add into pre-zeroed D) */
@@ -63,6 +63,12 @@ typedef struct dtm_update_config {
   int seg_offset[DTM_MAX_SEGMENTS + 1];
   float seg_wd[DTM_MAX_SEGMENTS];
   int seg_zero_grad[DTM_MAX_SEGMENTS]; /* 1: gradient is accumulated with atomics and must be cleared after use */
+  /* Optional: while writing the bf16 copy of segment `pack_seg` (the conv2 filter, [5][5][32][64]) also emit the two
+   * tensor-core operand images of dtm_conv2_pack_weights, so that no separate packing pass is needed.  -1 = off. */
+  int pack_seg;
+  int reserved2;
+  void* pack_fwd;
+  void* pack_dgrad;
 } dtm_update_config;
 
 /* Peer-memory communication context, passed to kernels by value: base pointers of every rank's symmetric buffers
@@ -111,12 +117,17 @@ int dtm_conv1_wgrad(const void* x, int in_is_float, int channels, const void* gr
 /* ---- conv2 on tcgen05 (reference: mnist_input.py:156-172) ------------------------------------------------------ */
 /* w2_bf16: bf16 copy of the TF-layout weights [5][5][32][64].  p2: bf16 [B][7][7][64] (== [B][3136] in TF flatten
  * order), argmax uint8 same shape, act2 bf16 [B][196][64] (only with lrn: post-ReLU, pre-LRN activation). */
-int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const float* bias, int batch, int lrn, void* p2,
-                  void* argmax, void* act2, void* stream);
+int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const void* packed, const float* bias, int batch, int lrn,
+                  void* p2, void* argmax, void* act2, void* stream);
+/* Re-packs the bf16 conv2 weights into the two shared-memory operand images the tensor-core kernels use
+ * (forward: [k/8][co][8], k = tap*32+ci; dgrad: [k/8][ci][8], k = (24-tap)*64+co), 102400 bytes each, so that each CTA
+ * fetches its weights with one bulk copy instead of re-packing them itself.  Pass the results as `packed` below
+ * (NULL = let the kernel pack from w2_bf16). */
+int dtm_conv2_pack_weights(const void* w2_bf16, void* packed_fwd, void* packed_dgrad, void* stream);
 /* dz2_planes: plane layout, 64 ch (from dtm_unpool2).  dpool1: bf16 [B][196][32], gradient w.r.t. conv1's pooled
  * activation with the ReLU mask (and LRN backward when lrn) applied. */
-int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, const void* p1_planes, const void* pool_raw, int batch,
-                    int lrn, void* dpool1, void* stream);
+int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, const void* packed, const void* p1_planes,
+                    const void* pool_raw, int batch, int lrn, void* dpool1, void* stream);
 /* dw2 fp32 [5][5][32][64], accumulated (red.add): zero on entry. */
 int dtm_conv2_wgrad(const void* p1_planes, const void* dz2_planes, int batch, float* dw2, void* stream);
 /* dp2 bf16 [B][49][64] -> dz2_planes (every byte of the valid region is written) ; db2[64] accumulated. */
@@ -140,6 +151,12 @@ int dtm_head_backward(const void* h, int batch, int hidden, const float* w, cons
  * global_step++.  grad_scale multiplies the summed gradient (1/world_size).  slot0/slot1/ema/w_bf16 may be NULL. */
 int dtm_fused_update(const dtm_update_config* cfg, dtm_train_state* state, float* w, float* grad, float* slot0,
                      float* slot1, float* ema, void* w_bf16, float grad_scale, void* stream);
+/* Same for the flat elements [lo, hi) only (multiples of 64).  Lets a caller update a bucket of variables as soon as
+ * its gradients are complete, beside the rest of the backward pass; only the call with do_finish = 1 closes the step.
+ * max_ctas > 0 caps the grid so that the kernel leaves room for the kernels it is meant to overlap with. */
+int dtm_fused_update_range(const dtm_update_config* cfg, dtm_train_state* state, float* w, float* grad, float* slot0,
+                           float* slot1, float* ema, void* w_bf16, float grad_scale, int lo, int hi, int do_finish,
+                           int max_ctas, void* stream);
 int dtm_state_init(dtm_train_state* state, long long global_step, float beta1, float beta2, void* stream);
 
 /* ---- summary statistics (reference: main.py:95-109 through monitor_cb) ----------------------------------------- */

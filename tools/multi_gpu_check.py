@@ -166,7 +166,7 @@ def main() -> int:
     for _ in range(8):
         count = [0]
         ref._forward(ref.x[0], ref.y[0], training=True, state=ref.state, count=count)
-        ref._backward(ref.x[0], count)
+        ref._backward(ref.x[0], count, with_comm=False)
         dist.all_reduce(ref.flat.grad)
         native.fused_update(ref.cfg, ref.state, ref.flat.w, ref.flat.grad, ref.flat.slot0, ref.flat.slot1, ref.flat.ema,
                             ref.flat.w_bf16, grad_scale=1.0 / world)
