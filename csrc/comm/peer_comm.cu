@@ -151,7 +151,6 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   const UpdateScalars u = make_update_scalars(cfg, st, 1.0f / static_cast<float>(N));
   float* w_local = ctx.w[r];
   float* g_local = ctx.grad[r];
-  (void)g_local;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   const int nthreads = gridDim.x * blockDim.x;
 
@@ -193,24 +192,42 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
     const float4 wv = *reinterpret_cast<const float4*>(w_local + i);
     const float4 o = update_vec4(cfg, u, wv, g, wd, slot0, slot1, ema, i);
     *reinterpret_cast<float4*>(w_local + i) = o;
+    if (cfg.seg_gather_bf16[seg]) {
+      // tensor-core-only variable: peers need the bf16 value, nothing else (half the link bytes, no conversion pass)
+      const uint2 pk = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
 #pragma unroll 1
-    for (int j = 1; j < N; ++j) {   // start with the next rank so that the N ranks do not all hit the same peer
-      const int p = (r + j) % N;
-      st_peer_v4(ctx.w[p] + i, o);
+      for (int j = 0; j < N; ++j) {   // start with this rank itself, then walk the ring
+        const int p = (r + j) % N;
+        asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1,%2};" ::"l"(static_cast<__nv_bfloat16*>(ctx.w_bf16[p]) + i), "r"(pk.x), "r"(pk.y) : "memory");
+      }
+    } else {
+#pragma unroll 1
+      for (int j = 1; j < N; ++j) {   // start with the next rank so that the N ranks do not all hit the same peer
+        const int p = (r + j) % N;
+        st_peer_v4(ctx.w[p] + i, o);
+      }
     }
   }
 
   // ---- barrier B: all shards of the new weights have landed everywhere, nobody reads my gradients any more
   cross_gpu_barrier(ctx, ctrl, e0 + 2);
 
-  // ---- local pass over the whole bucket: bf16 shadow weights, clear accumulated gradients
-  seg = 0;
-  for (int i = lo + tid * 4; i < hi; i += nthreads * 4) {
-    const float4 v = *reinterpret_cast<const float4*>(w_local + i);
-    *reinterpret_cast<uint2*>(w_bf16 + i) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
-    seg = segment_advance(cfg, seg, i);
-    if (seg == cfg.pack_seg) pack_conv2_vec4(cfg, i - cfg.seg_offset[seg], v);
-    if (cfg.seg_zero_grad[seg]) *reinterpret_cast<float4*>(g_local + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+  // ---- local pass, only over the variables that were gathered in fp32 (the small ones): bf16 shadow, operand images,
+  //      and clearing of gradients that are accumulated with atomics
+  for (int s = 0; s < cfg.n_segments; ++s) {
+    const int a = max(lo, cfg.seg_offset[s]), b = min(hi, cfg.seg_offset[s + 1]);
+    if (a >= b) continue;
+    const bool convert = !cfg.seg_gather_bf16[s];
+    const bool zero = cfg.seg_zero_grad[s] != 0;
+    if (!convert && !zero) continue;
+    for (int i = a + tid * 4; i < b; i += nthreads * 4) {
+      if (convert) {
+        const float4 v = *reinterpret_cast<const float4*>(w_local + i);
+        *reinterpret_cast<uint2*>(w_bf16 + i) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+        if (s == cfg.pack_seg) pack_conv2_vec4(cfg, i - cfg.seg_offset[s], v);
+      }
+      if (zero) *reinterpret_cast<float4*>(g_local + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
   }
 
   __threadfence();

@@ -120,6 +120,7 @@ class FlatParams:
             cfg.seg_offset[i] = self.offsets[v.name]
             cfg.seg_wd[i] = float(v.wd or 0.0)
             cfg.seg_zero_grad[i] = 1 if v.atomic_grad else 0
+            cfg.seg_gather_bf16[i] = 1 if v.tensor_core_only else 0
         cfg.seg_offset[len(self.spec.variables)] = self.total
         cfg.pack_seg = -1
         return cfg

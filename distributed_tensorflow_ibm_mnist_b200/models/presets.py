@@ -37,6 +37,12 @@ class VarSpec:
     def layer(self) -> str:
         return self.name.split("/")[0]
 
+    @property
+    def tensor_core_only(self) -> bool:
+        """The big fc matrices are read by the GEMM kernels only (as bf16): with several GPUs their fp32 master stays on
+        the owning rank and only bf16 travels over NVLink."""
+        return not self.atomic_grad
+
 
 @dataclass(frozen=True)
 class ModelSpec:

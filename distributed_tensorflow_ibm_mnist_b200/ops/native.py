@@ -62,6 +62,7 @@ class UpdateConfig(ctypes.Structure):
         ("seg_offset", c_int * (MAX_SEGMENTS + 1)),
         ("seg_wd", c_float * MAX_SEGMENTS),
         ("seg_zero_grad", c_int * MAX_SEGMENTS),
+        ("seg_gather_bf16", c_int * MAX_SEGMENTS),
         ("pack_seg", c_int), ("reserved2", c_int), ("pack_fwd", c_void_p), ("pack_dgrad", c_void_p),
     ]
 

@@ -34,7 +34,7 @@ class PeerCtx(ctypes.Structure):
     """Mirror of ``dtm_peer_ctx``."""
 
     _fields_ = [("rank", c_int), ("world", c_int), ("grad", c_void_p * MAX_RANKS), ("w", c_void_p * MAX_RANKS),
-                ("flags", c_void_p * MAX_RANKS)]
+                ("flags", c_void_p * MAX_RANKS), ("w_bf16", c_void_p * MAX_RANKS)]
 
 
 class _CudaBuffer:
@@ -98,6 +98,7 @@ class PeerComm:
         self.ctrl = torch.zeros(16, dtype=torch.uint8, device=self.device)
         self.w_buf: SymmetricBuffer | None = None
         self.grad_buf: SymmetricBuffer | None = None
+        self.bf16_buf: SymmetricBuffer | None = None
         self.ctx: PeerCtx | None = None
         self._scratch: SymmetricBuffer | None = None
         self._scratch_ctx: PeerCtx | None = None
@@ -117,25 +118,29 @@ class PeerComm:
             if name == "grad":
                 self.grad_buf = self._alloc(n * 4)
                 return self.grad_buf.view(torch.float32, n)
+            if name == "w_bf16":
+                self.bf16_buf = self._alloc(n * 2)
+                return self.bf16_buf.view(torch.bfloat16, n)
             return torch.zeros(n, dtype=dtype, device=self.device)
 
         alloc.named = True
         return alloc
 
-    def _make_ctx(self, grad: SymmetricBuffer | None, w: SymmetricBuffer | None) -> PeerCtx:
+    def _make_ctx(self, grad: SymmetricBuffer | None, w: SymmetricBuffer | None, bf16: SymmetricBuffer | None = None) -> PeerCtx:
         c = PeerCtx()
         c.rank, c.world = self.rank, self.world_size
         for j in range(self.world_size):
             c.grad[j] = grad.ptrs[j] if grad else 0
             c.w[j] = w.ptrs[j] if w else 0
+            c.w_bf16[j] = bf16.ptrs[j] if bf16 else 0
             c.flags[j] = self.flags.ptrs[j]
         return c
 
     def _ensure_ctx(self) -> PeerCtx:
         if self.ctx is None:
-            if self.w_buf is None or self.grad_buf is None:
+            if self.w_buf is None or self.grad_buf is None or self.bf16_buf is None:
                 raise RuntimeError("PeerComm: FlatParams must be created with comm.flat_allocator() first")
-            self.ctx = self._make_ctx(self.grad_buf, self.w_buf)
+            self.ctx = self._make_ctx(self.grad_buf, self.w_buf, self.bf16_buf)
             dist.barrier(group=self.group)   # every rank has mapped every buffer before the first kernel touches a peer
         return self.ctx
 

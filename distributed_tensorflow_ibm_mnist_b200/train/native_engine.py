@@ -117,7 +117,8 @@ class NativeEngine:
         return self.comm is not None and self.world > 1
 
     def params(self) -> dict[str, torch.Tensor]:
-        return {k: v.cpu() for k, v in self.flat.to_dict().items()}
+        # sharded engines keep the fp32 master of the big fc matrices on the owning rank only (collective gather)
+        return self._full(self.flat.w) if self.sharded else {k: v.cpu() for k, v in self.flat.to_dict().items()}
 
     def _full(self, buf: torch.Tensor) -> dict[str, torch.Tensor]:
         if self.sharded:   # collective: every rank must call
@@ -371,7 +372,9 @@ class NativeEngine:
         self.forward_backward(slot)
         grads = {v.name: self.flat.gradient(v.name).clone() for v in self.spec.variables}
         self.flat.grad.zero_()
-        params = {v.name: self.flat.weight(v.name) for v in self.spec.variables}
+        # the bf16 shadow is current on every rank even where the fp32 master lives elsewhere (sharded fc matrices)
+        params = {v.name: (self.flat.weight_bf16(v.name).float() if self.sharded and v.tensor_core_only else self.flat.weight(v.name))
+                  for v in self.spec.variables}
         return {"params": params, "activations": self.activations(), "gradients": grads}
 
     def scalar_state(self) -> dict:

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define DTM_ABI_VERSION 3
+#define DTM_ABI_VERSION 4
 
 /* GEMM epilogues */
 #define DTM_EPI_STORE_F32 0      /* D(fp32)  = alpha * acc          (split-K: red.add into pre-zeroed D) */
@@ -65,6 +65,10 @@ typedef struct dtm_update_config {
   int seg_zero_grad[DTM_MAX_SEGMENTS]; /* 1: gradient is accumulated with atomics and must be cleared after use */
   /* Optional: while writing the bf16 copy of segment `pack_seg` (the conv2 filter, [5][5][32][64]) also emit the two
    * tensor-core operand images of dtm_conv2_pack_weights, so that no separate packing pass is needed.  -1 = off. */
+  /* Multi-GPU only: 1 = after the update the owner sends just the bf16 value of this variable to its peers (the
+   * variable is consumed by tensor-core kernels only); the fp32 master then lives on the owning rank alone and is
+   * gathered on demand (checkpoints).  0 = the fp32 value is all-gathered and every rank derives bf16 locally. */
+  int seg_gather_bf16[DTM_MAX_SEGMENTS];
   int pack_seg;
   int reserved2;
   void* pack_fwd;
@@ -79,6 +83,7 @@ typedef struct dtm_peer_ctx {
   float* grad[DTM_MAX_RANKS];
   float* w[DTM_MAX_RANKS];
   unsigned int* flags[DTM_MAX_RANKS]; /* DTM_MAX_RANKS epochs per rank; slot r of rank p is written by rank r */
+  void* w_bf16[DTM_MAX_RANKS];        /* bf16 shadow weights (symmetric): target of the bf16-only all-gather */
 } dtm_peer_ctx;
 
 /* ---- runtime ---------------------------------------------------------------------------------- */
@@ -188,8 +193,9 @@ int dtm_symm_open(const unsigned char* handle64, void** peer_ptr);
 int dtm_symm_close(void* peer_ptr);
 int dtm_symm_free(void* ptr);
 /* One kernel: cross-GPU barrier, reduce-scatter of grad[lo:hi) over peer loads, scale 1/N + weight decay + optimizer
- * + EMA on this rank's shard, all-gather of the new fp32 weights by peer stores, barrier, bf16 shadow + gradient
- * clearing; with do_finish the step bookkeeping of dtm_fused_update.  `ctrl` = 16 bytes of zero-initialised device
+ * + EMA on this rank's shard, all-gather of the new weights by peer stores (bf16 only for seg_gather_bf16 variables,
+ * fp32 otherwise), barrier, local bf16 shadow of the fp32-gathered variables + gradient clearing; with do_finish the
+ * step bookkeeping of dtm_fused_update.  `ctrl` = 16 bytes of zero-initialised device
  * memory per communicator.  max_ctas > 0 caps the grid (use when the kernel overlaps with compute kernels).
  * All ranks must issue the same sequence of collectives. */
 int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_update_config* cfg, dtm_train_state* state, int lo, int hi,

@@ -119,9 +119,11 @@ def main() -> int:
                                 grad_scale=1.0 / world)
             torch.cuda.synchronize()
         tol = 3e-4 if kind == "adam" else 2e-6
-        err = float((flat_a.w - flat_b.w).abs().max() / flat_b.w.abs().max())
+        buckets = [(split, flat_a.total), (0, split)]
+        full_w = comm.gather_sharded(flat_a.w, buckets)       # fp32 masters of the big fc matrices live on their owners
+        err = float((full_w - flat_b.w).abs().max() / flat_b.w.abs().max())
         check(f"fused_update_{kind}_weights", err < tol, err)
-        check(f"fused_update_{kind}_bf16", torch.equal(flat_a.w_bf16, flat_a.w.to(torch.bfloat16)))
+        check(f"fused_update_{kind}_bf16", torch.equal(flat_a.w_bf16, full_w.to(torch.bfloat16)))
         lo, hi = comm.shard_range(split, flat_a.total, rank)
         e_err = float((flat_a.ema[lo:hi] - flat_b.ema[lo:hi]).abs().max() / flat_b.ema.abs().max())
         check(f"fused_update_{kind}_ema_shard", e_err < tol, e_err)
@@ -130,10 +132,10 @@ def main() -> int:
               abs(sa.last_wl[4] - sb.last_wl[4]) <= 1e-4 * abs(sb.last_wl[4]) + 1e-9, (sa.global_step, sa.last_wl[4], sb.last_wl[4]))
         zero_ok = float(flat_a.gradient("conv2/weights").abs().sum()) == 0.0 and float(flat_a.gradient("local3/weights").abs().sum()) > 0
         check(f"fused_update_{kind}_grad_clearing", zero_ok)
-        w0 = flat_a.w.clone()
+        w0 = flat_a.w_bf16.clone()
         dist.broadcast(w0, src=0)
-        check(f"fused_update_{kind}_ranks_agree_bitwise", torch.equal(w0, flat_a.w))
-        full_ema = comm.gather_sharded(flat_a.ema, [(split, flat_a.total), (0, split)])
+        check(f"fused_update_{kind}_ranks_agree_bitwise", torch.equal(w0, flat_a.w_bf16))
+        full_ema = comm.gather_sharded(flat_a.ema, buckets)
         check(f"fused_update_{kind}_gather_sharded", float((full_ema - flat_b.ema).abs().max() / flat_b.ema.abs().max()) < tol)
 
     # ---- broadcast + real training steps through the engine -------------------------------------------------
@@ -149,30 +151,50 @@ def main() -> int:
     x = torch.randint(0, 256, (64, 784), dtype=torch.uint8, generator=g).to(dev)
     y = torch.randint(0, 10, (64,), dtype=torch.int32, generator=g).to(dev)
     eng.stage_batch(0, x, y)
-    losses = []
-    for _ in range(8):
-        eng.train_step(0)
-        losses.append(eng.metrics()["cross_entropy"])
-    w0 = eng.flat.w.clone()
-    dist.broadcast(w0, src=0)
-    m = eng.metrics()
-    check("engine_ranks_agree_bitwise", torch.equal(w0, eng.flat.w), m["global_step"])
-    check("engine_loss_decreases", losses[-1] < losses[0] and m["global_step"] == 8 and not m["nan"], losses)
-    # the same 8 steps, single process semantics: average of the per-rank gradients == what one big batch would give;
-    # cross-check against an un-fused run: engine without comm + NCCL all-reduce of gradients + fused_update(1/N)
+    # cross-check against an un-fused run of the same steps: engine without comm + NCCL all-reduce of the gradients +
+    # single-GPU fused update with grad_scale = 1/N.  Different data per rank; compared after the first step (tight: only
+    # summation order differs) and after 8 steps (loose: ReLU / dropout decisions amplify rounding differences).
     ref = NativeEngine(spec, 64, device=dev, optimizer="momentum", base_lr=0.02, seed=11, use_graph=False)
     ref.load_params(oracle.init_params(spec, seed=0))
     ref.stage_batch(0, x, y)
-    for _ in range(8):
+
+    def ref_step():
         count = [0]
         ref._forward(ref.x[0], ref.y[0], training=True, state=ref.state, count=count)
         ref._backward(ref.x[0], count, with_comm=False)
         dist.all_reduce(ref.flat.grad)
         native.fused_update(ref.cfg, ref.state, ref.flat.w, ref.flat.grad, ref.flat.slot0, ref.flat.slot1, ref.flat.ema,
                             ref.flat.w_bf16, grad_scale=1.0 / world)
-    torch.cuda.synchronize()
-    err = float((eng.flat.w - ref.flat.w).abs().max() / ref.flat.w.abs().max())
-    check("engine_matches_nccl_path", err < 1e-3, err)
+
+    def rel_err():
+        torch.cuda.synchronize()
+        full = comm.gather_sharded(eng.flat.w, eng.buckets)
+        return float((full - ref.flat.w).abs().max() / ref.flat.w.abs().max())
+
+    eng.train_step(0)
+    ref_step()
+    e1 = rel_err()
+    check("engine_matches_nccl_path_step1", e1 < 2e-5, e1)
+    for _ in range(7):
+        eng.train_step(0)
+        ref_step()
+    e8 = rel_err()
+    check("engine_matches_nccl_path_step8", e8 < 5e-2, e8)
+    w0 = eng.flat.w_bf16.clone()
+    dist.broadcast(w0, src=0)
+    m = eng.metrics()
+    check("engine_ranks_agree_bitwise", torch.equal(w0, eng.flat.w_bf16), m["global_step"])
+    # learning: identical data on every rank (the averaged gradient is then the single-GPU gradient), same path
+    g = torch.Generator(device="cpu").manual_seed(4242)
+    xs = torch.randint(0, 256, (64, 784), dtype=torch.uint8, generator=g).to(dev)
+    ys = torch.randint(0, 10, (64,), dtype=torch.int32, generator=g).to(dev)
+    eng.stage_batch(0, xs, ys)
+    losses = []
+    for _ in range(10):
+        eng.train_step(0)
+        losses.append(eng.metrics()["cross_entropy"])
+    m = eng.metrics()
+    check("engine_loss_decreases", losses[-1] < losses[0] and m["global_step"] == 18 and not m["nan"], losses)
 
     # ---- bandwidth sweep vs NCCL ------------------------------------------------------------------------------
     if args.sweep:
