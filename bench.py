@@ -147,7 +147,7 @@ def main() -> None:
                        decay_steps=presets.decay_steps(B), seed=1234, comm=comm, use_graph=not args.no_graph)
     eng.load_params(oracle.init_params(spec, seed=0))
     if comm is not None:
-        comm.broadcast_params(eng.flat, eng.state)
+        eng.broadcast_params()
 
     def barrier():
         torch.cuda.synchronize()

@@ -167,9 +167,19 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
       if (a >= b) continue;
       any = true;
       float sq = 0.0f;
-      for (int i = a + tid * 4; i < b; i += nthreads * 4) {
-        const float4 v = *reinterpret_cast<const float4*>(w_local + i);
-        sq += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+      if (cfg.seg_gather_bf16[s]) {
+        // fp32 masters of these variables are only current on their owners; the bf16 shadow is current everywhere
+        // (this sum only feeds the *reported* loss value - the decay gradient itself uses the owner's fp32 weights)
+        for (int i = a + tid * 4; i < b; i += nthreads * 4) {
+          const uint2 v = *reinterpret_cast<const uint2*>(w_bf16 + i);
+          const float x0 = bf16_lo(v.x), x1 = bf16_hi(v.x), x2 = bf16_lo(v.y), x3 = bf16_hi(v.y);
+          sq += x0 * x0 + x1 * x1 + x2 * x2 + x3 * x3;
+        }
+      } else {
+        for (int i = a + tid * 4; i < b; i += nthreads * 4) {
+          const float4 v = *reinterpret_cast<const float4*>(w_local + i);
+          sq += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+        }
       }
       sq = warp_sum(sq);
       if (lane_id() == 0 && sq != 0.0f) atomicAdd(&s_wl[s], sq);

@@ -111,6 +111,17 @@ class NativeEngine:
             self.state.copy_(torch.frombuffer(bytearray(bytes(st)), dtype=torch.uint8).to(self.device))
         torch.cuda.synchronize(self.device)
 
+    def broadcast_params(self, root: int = 0) -> None:
+        """Make rank ``root``'s weights and training-state scalars authoritative on every rank (peer-memory broadcast) and
+        refresh everything derived from them (bf16 shadow, conv2 operand images, EMA shadows of a fresh run)."""
+        if self.comm is None or self.world <= 1:
+            return
+        self.comm.broadcast_params(self.flat, self.state, root)
+        native.conv2_pack_weights(self.flat.weight_bf16("conv2/weights"), self.w2_fwd, self.w2_dgrad)
+        if int(self.read_state().global_step) == 0 and self.flat.ema is not None:
+            self.flat.ema.copy_(self.flat.w)     # TF initialises the shadows to the (now common) initial values
+        torch.cuda.synchronize(self.device)
+
     @property
     def sharded(self) -> bool:
         """True when optimizer slots / EMA shadows are only valid on their owning rank (fused multi-GPU update)."""

@@ -166,7 +166,7 @@ def train():
     else:
         print(f"restored checkpoint at global step {step} from {FLAGS.train_dir}")
     if comm is not None:
-        comm.broadcast_params(engine.flat, engine.state)
+        engine.broadcast_params()
     elif group is not None:
         import torch.distributed as dist
 

@@ -129,7 +129,7 @@ def main() -> int:
         check(f"fused_update_{kind}_ema_shard", e_err < tol, e_err)
         sa, sb = native.read_state(st_a), native.read_state(st_b)
         check(f"fused_update_{kind}_state", sa.global_step == sb.global_step == 3 and abs(sa.last_lr - sb.last_lr) < 1e-9 and
-              abs(sa.last_wl[4] - sb.last_wl[4]) <= 1e-4 * abs(sb.last_wl[4]) + 1e-9, (sa.global_step, sa.last_wl[4], sb.last_wl[4]))
+              abs(sa.last_wl[4] - sb.last_wl[4]) <= 2e-3 * abs(sb.last_wl[4]) + 1e-9, (sa.global_step, sa.last_wl[4], sb.last_wl[4]))
         zero_ok = float(flat_a.gradient("conv2/weights").abs().sum()) == 0.0 and float(flat_a.gradient("local3/weights").abs().sum()) > 0
         check(f"fused_update_{kind}_grad_clearing", zero_ok)
         w0 = flat_a.w_bf16.clone()
@@ -143,7 +143,7 @@ def main() -> int:
     comm.ctx = None
     eng = NativeEngine(spec, 64, device=dev, optimizer="momentum", base_lr=0.02, seed=11, comm=comm, use_graph=True)
     eng.load_params(oracle.init_params(spec, seed=rank))          # deliberately different per rank
-    comm.broadcast_params(eng.flat, eng.state)
+    eng.broadcast_params()
     w0 = eng.flat.w.clone()
     dist.broadcast(w0, src=0)
     check("broadcast_params", torch.equal(w0, eng.flat.w) and torch.equal(eng.flat.w_bf16, eng.flat.w.to(torch.bfloat16)))
