@@ -72,9 +72,9 @@ def forward(params: dict[str, torch.Tensor], images: torch.Tensor, spec: ModelSp
     """
     q = emulate_bf16
     B = images.shape[0]
-    x = images.view(B, 28, 28, spec.channels).permute(0, 3, 1, 2)
+    x = _q(images, q).view(B, 28, 28, spec.channels).permute(0, 3, 1, 2)
     acts: dict[str, torch.Tensor] = {}
-    w1 = params["conv1/weights"].permute(3, 2, 0, 1)
+    w1 = _q(params["conv1/weights"], q).permute(3, 2, 0, 1)
     a1 = F.relu(F.conv2d(x, w1, params["conv1/biases"], padding=2))
     acts["conv1"] = a1
     p1 = F.max_pool2d(a1, 2)
