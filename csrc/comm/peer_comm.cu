@@ -60,6 +60,21 @@ DTM_DEVICE void st_peer_v4(float* p, float4 v) {
   asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+// NVLS (NVLink SHARP) through a multicast address: one load that the NVSwitch answers with the SUM of every rank's copy,
+// one store that the switch replicates into every rank's copy.
+DTM_DEVICE float4 mc_ld_reduce_v4(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+DTM_DEVICE void mc_st_v4(float* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+DTM_DEVICE void mc_st_bf16x4(__nv_bfloat16* p, uint32_t a, uint32_t b) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+
 // Ranks may reach a collective seconds apart (start-up, graph capture), so cross-GPU waits get a longer leash than
 // the intra-kernel pipelines: ~2 minutes of SM clocks.
 constexpr long long COMM_WATCHDOG_CYCLES = 240000000000ll;
@@ -194,9 +209,10 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   // ---- reduce-scatter + optimizer on my shard + all-gather of the new weights
   int s_lo, s_hi;
   shard_range(lo, hi, r, N, s_lo, s_hi);
+  const bool nvls = ctx.mc_grad != nullptr && ctx.mc_w != nullptr && ctx.mc_w_bf16 != nullptr;
   int seg = 0;
-  for (int i = s_lo + tid * 4; i < s_hi; i += nthreads * 4) {
-    const float4 g = reduce_peers(ctx.grad, N, i);
+  // optimizer + EMA on one float4 of my shard, then publish it: multicast store (NVLS) or N-1 peer stores (P2P)
+  auto apply = [&](int i, const float4 g) {
     seg = segment_advance(cfg, seg, i);
     const float wd = cfg.seg_wd[seg];
     const float4 wv = *reinterpret_cast<const float4*>(w_local + i);
@@ -205,11 +221,17 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
     if (cfg.seg_gather_bf16[seg]) {
       // tensor-core-only variable: peers need the bf16 value, nothing else (half the link bytes, no conversion pass)
       const uint2 pk = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+      if (nvls) {
+        mc_st_bf16x4(static_cast<__nv_bfloat16*>(ctx.mc_w_bf16) + i, pk.x, pk.y);
+      } else {
 #pragma unroll 1
-      for (int j = 0; j < N; ++j) {   // start with this rank itself, then walk the ring
-        const int p = (r + j) % N;
-        asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1,%2};" ::"l"(static_cast<__nv_bfloat16*>(ctx.w_bf16[p]) + i), "r"(pk.x), "r"(pk.y) : "memory");
+        for (int j = 0; j < N; ++j) {   // start with this rank itself, then walk the ring
+          const int p = (r + j) % N;
+          asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1,%2};" ::"l"(static_cast<__nv_bfloat16*>(ctx.w_bf16[p]) + i), "r"(pk.x), "r"(pk.y) : "memory");
+        }
       }
+    } else if (nvls) {
+      mc_st_v4(ctx.mc_w + i, o);
     } else {
 #pragma unroll 1
       for (int j = 1; j < N; ++j) {   // start with the next rank so that the N ranks do not all hit the same peer
@@ -217,6 +239,33 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
         st_peer_v4(ctx.w[p] + i, o);
       }
     }
+  };
+  const int step = nthreads * 4;
+  if (nvls) {
+    // four in-switch reductions in flight per thread before the first one is consumed
+    constexpr int U = 4;
+    for (int base = s_lo + tid * 4; base < s_hi; base += step * U) {
+      float4 g[U];
+#pragma unroll
+      for (int k = 0; k < U; ++k)
+        if (base + k * step < s_hi) g[k] = mc_ld_reduce_v4(ctx.mc_grad + base + k * step);
+#pragma unroll
+      for (int k = 0; k < U; ++k)
+        if (base + k * step < s_hi) apply(base + k * step, g[k]);
+    }
+  } else if (N == 8 || N == 4 || N == 2) {
+    // two float4 per thread and iteration: 2(N-1) NVLink round trips overlap, and the second one hides the optimizer
+    // math of the first
+    for (int base = s_lo + tid * 4; base < s_hi; base += step * 2) {
+      const bool two = base + step < s_hi;
+      const float4 g0 = reduce_peers(ctx.grad, N, base);
+      float4 g1 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (two) g1 = reduce_peers(ctx.grad, N, base + step);
+      apply(base, g0);
+      if (two) apply(base + step, g1);
+    }
+  } else {
+    for (int i = s_lo + tid * 4; i < s_hi; i += step) apply(i, reduce_peers(ctx.grad, N, i));
   }
 
   // ---- barrier B: all shards of the new weights have landed everywhere, nobody reads my gradients any more
@@ -261,25 +310,48 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
 //   mode 0 (one-shot): out[i] = sum_j buf_j[i], every rank reads all peers.
 //   mode 1 (two-shot): shard owner reduces and writes the sum back into every rank's buf (in place); out = buf.
 __global__ void __launch_bounds__(512, 1)
-allreduce_kernel(const dtm_peer_ctx ctx, float* const* __restrict__ bufs, int off, int n, float* __restrict__ out,
-                 int mode, CommCtrl* __restrict__ ctrl) {
+allreduce_kernel(const dtm_peer_ctx ctx, float* const* __restrict__ bufs, float* __restrict__ mc, int off, int n,
+                 float* __restrict__ out, int mode, CommCtrl* __restrict__ ctrl) {
   const int N = ctx.world, r = ctx.rank;
   const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   const int nthreads = gridDim.x * blockDim.x;
   cross_gpu_barrier(ctx, ctrl, e0 + 1);
+  const int step = nthreads * 4;
   if (mode == 0) {
-    for (int i = tid * 4; i < n; i += nthreads * 4) {
-      const float4 a = reduce_peers(bufs, N, off + i);
-      *reinterpret_cast<float4*>(out + i) = a;
+    if (mc) {
+      // NVLS one-shot: every rank asks the switch for the sum of every element
+      for (int base = tid * 4; base < n; base += step * 4) {
+        float4 a[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (base + k * step < n) a[k] = mc_ld_reduce_v4(mc + off + base + k * step);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (base + k * step < n) *reinterpret_cast<float4*>(out + base + k * step) = a[k];
+      }
+    } else {
+      for (int i = tid * 4; i < n; i += step) {
+        const float4 a = reduce_peers(bufs, N, off + i);
+        *reinterpret_cast<float4*>(out + i) = a;
+      }
     }
   } else {
     int s_lo, s_hi;
     shard_range(0, n, r, N, s_lo, s_hi);
-    for (int i = s_lo + tid * 4; i < s_hi; i += nthreads * 4) {
-      const float4 a = reduce_peers(bufs, N, off + i);
+    if (mc) {
+      // NVLS two-shot: in-switch reduction of my shard, multicast store of the sums into every rank's buffer
+      for (int base = s_lo + tid * 4; base < s_hi; base += step * 4) {
+        float4 a[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (base + k * step < s_hi) a[k] = mc_ld_reduce_v4(mc + off + base + k * step);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (base + k * step < s_hi) mc_st_v4(mc + off + base + k * step, a[k]);
+      }
+    } else {
+      for (int i = s_lo + tid * 4; i < s_hi; i += step) {
+        const float4 a = reduce_peers(bufs, N, off + i);
 #pragma unroll 1
-      for (int j = 0; j < N; ++j) st_peer_v4(bufs[(r + j) % N] + off + i, a);
+        for (int j = 0; j < N; ++j) st_peer_v4(bufs[(r + j) % N] + off + i, a);
+      }
     }
   }
   cross_gpu_barrier(ctx, ctrl, e0 + 2);
@@ -392,15 +464,15 @@ extern "C" int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_upd
                             static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish);
 }
 
-extern "C" int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, int off, int n, float* out, int mode, void* ctrl,
-                                 void* stream) {
+extern "C" int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, float* mc_buf, int off, int n, float* out, int mode,
+                                 void* ctrl, void* stream) {
   using namespace dtm;
   if (int rc = check_ctx(ctx)) return rc;
   if (n <= 0 || n % 4 || off % 4) return dtm_fail("allreduce: n and offset must be positive multiples of 4");
   if (mode != 0 && mode != 1) return dtm_fail("allreduce: mode 0 (one-shot) or 1 (two-shot)");
   const size_t work = mode == 0 ? static_cast<size_t>(n) : static_cast<size_t>(n) / ctx->world + 1;
-  return launch_cooperative(allreduce_kernel, comm_grid(work), 512, static_cast<cudaStream_t>(stream), *ctx, bufs_dev, off, n, out,
-                            mode, static_cast<CommCtrl*>(ctrl));
+  return launch_cooperative(allreduce_kernel, comm_grid(work), 512, static_cast<cudaStream_t>(stream), *ctx, bufs_dev, mc_buf, off, n,
+                            out, mode, static_cast<CommCtrl*>(ctrl));
 }
 
 extern "C" int dtm_broadcast_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, int off, int n, int root, void* ctrl, void* stream) {

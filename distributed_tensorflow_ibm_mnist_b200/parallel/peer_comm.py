@@ -1,7 +1,8 @@
 """PeerComm — the NVLink peer-memory communicator (python side of csrc/comm/peer_comm.cu).
 
-``torch.distributed`` is only the control plane here: it carries the 64-byte CUDA IPC handles once at start-up and is
-used for rare, cold operations (gathering sharded optimizer state for a checkpoint).  Every hot collective — the
+``torch.distributed`` is only the control plane here: it sets up the symmetric buffers once at start-up (either torch's
+symmetric-memory rendezvous, which also yields an NVLS multicast address when the NVSwitch offers one, or our own CUDA
+IPC handle exchange) and is used for rare, cold operations (gathering sharded optimizer state for a checkpoint).  Every hot collective — the
 gradient all-reduce fused with the optimizer, the initial parameter / global_step broadcast, the stand-alone
 all-reduce — is one of our own kernels reading and writing peer GPU memory directly.
 
@@ -11,6 +12,7 @@ mnist_input.py:262-264), chief initialisation + readiness polling (MonitoredTrai
 from __future__ import annotations
 
 import ctypes
+import os
 from ctypes import c_int, c_size_t, c_void_p
 
 import torch
@@ -26,7 +28,7 @@ _lib.register("dtm_symm_open", [P, P])
 _lib.register("dtm_symm_close", [P])
 _lib.register("dtm_symm_free", [P])
 _lib.register("dtm_fused_allreduce_update", [P, P, P, I, I, P, P, P, P, P, I, I, P])
-_lib.register("dtm_allreduce_f32", [P, P, I, I, P, I, P, P])
+_lib.register("dtm_allreduce_f32", [P, P, P, I, I, P, I, P, P])
 _lib.register("dtm_broadcast_f32", [P, P, I, I, I, P, P])
 
 
@@ -34,7 +36,8 @@ class PeerCtx(ctypes.Structure):
     """Mirror of ``dtm_peer_ctx``."""
 
     _fields_ = [("rank", c_int), ("world", c_int), ("grad", c_void_p * MAX_RANKS), ("w", c_void_p * MAX_RANKS),
-                ("flags", c_void_p * MAX_RANKS), ("w_bf16", c_void_p * MAX_RANKS)]
+                ("flags", c_void_p * MAX_RANKS), ("w_bf16", c_void_p * MAX_RANKS),
+                ("mc_grad", c_void_p), ("mc_w", c_void_p), ("mc_w_bf16", c_void_p)]
 
 
 class _CudaBuffer:
@@ -45,19 +48,31 @@ class _CudaBuffer:
 
 
 class SymmetricBuffer:
-    """One allocation per rank, mapped into every rank: ``local`` tensor + ``ptrs[j]`` = address of rank j's copy."""
+    """One allocation per rank, mapped into every rank: ``local`` tensor + ``ptrs[j]`` = address of rank j's copy.
+
+    ``mc_ptr`` is the NVLS multicast address of the buffer (0 when the communicator runs without multicast)."""
 
     def __init__(self, comm: "PeerComm", nbytes: int):
-        lib = _lib.load()
         self.comm, self.nbytes = comm, nbytes
+        self.mc_ptr = 0
+        self._opened: list[int] = []
+        self.base = 0
+        self._symm = None
+        if comm.nvls:
+            self._init_multicast()
+        else:
+            self._init_ipc()
+        self.ptrs_dev = torch.tensor(self.ptrs, dtype=torch.int64, device=comm.device)   # float* const* for the kernels
+
+    def _init_ipc(self) -> None:
+        lib, comm = _lib.load(), self.comm
         base = c_void_p()
         handle = (ctypes.c_ubyte * 64)()
-        check(lib.dtm_symm_alloc(nbytes, ctypes.byref(base), handle), "symm_alloc")
+        check(lib.dtm_symm_alloc(self.nbytes, ctypes.byref(base), handle), "symm_alloc")
         self.base = base.value
         handles: list = [None] * comm.world_size
         dist.all_gather_object(handles, bytes(handle), group=comm.group)
         self.ptrs: list[int] = []
-        self._opened: list[int] = []
         for j, h in enumerate(handles):
             if j == comm.rank:
                 self.ptrs.append(self.base)
@@ -67,8 +82,23 @@ class SymmetricBuffer:
             check(lib.dtm_symm_open(hb, ctypes.byref(peer)), f"symm_open(rank {j})")
             self.ptrs.append(peer.value)
             self._opened.append(peer.value)
-        self.local_u8 = torch.as_tensor(_CudaBuffer(self.base, nbytes), device=comm.device)
-        self.ptrs_dev = torch.tensor(self.ptrs, dtype=torch.int64, device=comm.device)   # float* const* for the kernels
+        self.local_u8 = torch.as_tensor(_CudaBuffer(self.base, self.nbytes), device=comm.device)
+
+    def _init_multicast(self) -> None:
+        """Allocation + peer mapping + multicast binding through torch's symmetric-memory plumbing (cuMem* VMM
+        allocations, handle exchange over the process group's store, cuMulticast* binding)."""
+        import torch.distributed._symmetric_memory as symm
+        comm = self.comm
+        t = symm.empty(self.nbytes, dtype=torch.uint8, device=comm.device)
+        h = symm.rendezvous(t, comm.group)
+        ptrs = [int(p) for p in h.buffer_ptrs]
+        mc = int(getattr(h, "multicast_ptr", 0) or 0)
+        if len(ptrs) != comm.world_size or ptrs[comm.rank] != t.data_ptr() or mc == 0:
+            raise RuntimeError("symmetric-memory rendezvous returned no usable multicast mapping")
+        t.zero_()
+        torch.cuda.synchronize(comm.device)
+        self._symm = (t, h)
+        self.local_u8, self.ptrs, self.mc_ptr = t, ptrs, mc
 
     def view(self, dtype: torch.dtype, numel: int | None = None) -> torch.Tensor:
         t = self.local_u8.view(dtype)
@@ -83,6 +113,29 @@ class SymmetricBuffer:
             self.local_u8 = None
             lib.dtm_symm_free(c_void_p(self.base))
             self.base = 0
+        self._symm = None
+
+
+def _nvls_available(group, device) -> bool:
+    """Collective decision: can every rank map a multicast buffer?  ``DTM_NVLS=0`` forces the P2P kernels."""
+    mode = os.environ.get("DTM_NVLS", "auto").lower()
+    if mode in ("0", "off", "false", "no"):
+        return False
+    ok = 1
+    try:
+        import torch.distributed._symmetric_memory as symm
+        t = symm.empty(4096, dtype=torch.uint8, device=device)
+        h = symm.rendezvous(t, group)
+        if not int(getattr(h, "multicast_ptr", 0) or 0):
+            ok = 0
+    except Exception:  # noqa: BLE001 - any failure means "use the IPC path"
+        ok = 0
+    flag = torch.tensor([ok], dtype=torch.int32, device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    avail = bool(flag.item())
+    if not avail and mode in ("1", "on", "true", "yes", "force"):
+        raise RuntimeError("DTM_NVLS=1 but NVLS multicast memory is not available on every rank")
+    return avail
 
 
 class PeerComm:
@@ -93,6 +146,8 @@ class PeerComm:
             raise ValueError(f"PeerComm supports up to {MAX_RANKS} ranks on one NVSwitch node")
         torch.cuda.set_device(self.device)
         self.overlap_ctas = overlap_ctas
+        self.nvls = _nvls_available(group, self.device)   # in-switch reduction + multicast stores (multimem.*)
+        self.use_multicast = self.nvls                    # the fused update takes the NVLS path (A/B switch for tools)
         self._buffers: list[SymmetricBuffer] = []
         self.flags = self._alloc(MAX_RANKS * 4 * 16)          # epochs, padded
         self.ctrl = torch.zeros(16, dtype=torch.uint8, device=self.device)
@@ -134,6 +189,8 @@ class PeerComm:
             c.w[j] = w.ptrs[j] if w else 0
             c.w_bf16[j] = bf16.ptrs[j] if bf16 else 0
             c.flags[j] = self.flags.ptrs[j]
+        if self.use_multicast and grad and w and bf16 and grad.mc_ptr and w.mc_ptr and bf16.mc_ptr:
+            c.mc_grad, c.mc_w, c.mc_w_bf16 = grad.mc_ptr, w.mc_ptr, bf16.mc_ptr
         return c
 
     def _ensure_ctx(self) -> PeerCtx:
@@ -182,11 +239,12 @@ class PeerComm:
             dist.barrier(group=self.group)
         return self._scratch
 
-    def all_reduce(self, x: torch.Tensor, mode: str = "auto") -> torch.Tensor:
+    def all_reduce(self, x: torch.Tensor, mode: str = "auto", nvls: bool | None = None) -> torch.Tensor:
         """Sum ``x`` (float32, numel % 4 == 0) over ranks through peer memory; returns a new tensor.
 
-        ``mode``: "one_shot" (every rank reads all peers), "two_shot" (reduce-scatter + all-gather) or "auto"
-        (one-shot up to 256 KiB, where latency dominates; two-shot above)."""
+        ``mode``: "one_shot" (every rank reads everything), "two_shot" (reduce-scatter + all-gather) or "auto"
+        (one-shot up to 256 KiB, where latency dominates; two-shot above).  ``nvls``: reduce inside the NVSwitch
+        through the multicast mapping (default: whenever the communicator has one)."""
         if x.dtype != torch.float32 or x.numel() % 4:
             raise ValueError("all_reduce: float32 with a multiple of 4 elements")
         n = x.numel()
@@ -195,12 +253,16 @@ class PeerComm:
         buf = self.scratch(n * 4)
         buf.view(torch.float32, n).copy_(x.reshape(-1))
         out = torch.empty_like(x)
-        self.all_reduce_inplace(buf, n, out, mode)
+        self.all_reduce_inplace(buf, n, out, mode, nvls)
         return out
 
-    def all_reduce_inplace(self, buf: SymmetricBuffer, n: int, out: torch.Tensor, mode: str) -> None:
-        check(_lib.load().dtm_allreduce_f32(ctypes.byref(self._scratch_ctx), ptr(buf.ptrs_dev), 0, n, ptr(out),
-                                            {"one_shot": 0, "two_shot": 1}[mode], ptr(self.ctrl), current_stream()), "all_reduce")
+    def all_reduce_inplace(self, buf: SymmetricBuffer, n: int, out: torch.Tensor, mode: str, nvls: bool | None = None) -> None:
+        use_mc = bool(buf.mc_ptr) if nvls is None else bool(nvls)
+        if use_mc and not buf.mc_ptr:
+            raise RuntimeError("all_reduce: this communicator has no multicast mapping (NVLS unavailable or DTM_NVLS=0)")
+        check(_lib.load().dtm_allreduce_f32(ctypes.byref(self._scratch_ctx), ptr(buf.ptrs_dev), c_void_p(buf.mc_ptr if use_mc else None),
+                                            0, n, ptr(out), {"one_shot": 0, "two_shot": 1}[mode], ptr(self.ctrl), current_stream()),
+              "all_reduce")
 
     # ---- cold path: assembling sharded optimizer state for checkpoints ---------------------------------------
     def shard_range(self, lo: int, hi: int, rank: int) -> tuple[int, int]:

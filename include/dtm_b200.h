@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define DTM_ABI_VERSION 4
+#define DTM_ABI_VERSION 5
 
 /* GEMM epilogues */
 #define DTM_EPI_STORE_F32 0      /* D(fp32)  = alpha * acc          (split-K: red.add into pre-zeroed D) */
@@ -84,6 +84,12 @@ typedef struct dtm_peer_ctx {
   float* w[DTM_MAX_RANKS];
   unsigned int* flags[DTM_MAX_RANKS]; /* DTM_MAX_RANKS epochs per rank; slot r of rank p is written by rank r */
   void* w_bf16[DTM_MAX_RANKS];        /* bf16 shadow weights (symmetric): target of the bf16-only all-gather */
+  /* NVLink-SHARP (NVLS) multicast addresses of the same three buffers, or NULL: one address that the NVSwitch maps onto
+   * every rank's copy.  When all three are set the collectives reduce inside the switch (multimem.ld_reduce) and
+   * all-gather with one multicast store (multimem.st) instead of N-1 peer loads / stores per element. */
+  float* mc_grad;
+  float* mc_w;
+  void* mc_w_bf16;
 } dtm_peer_ctx;
 
 /* ---- runtime ---------------------------------------------------------------------------------- */
@@ -202,9 +208,11 @@ int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_update_config*
                                float* slot0, float* slot1, float* ema, void* w_bf16, void* ctrl, int do_finish, int max_ctas,
                                void* stream);
 /* fp32 sum over ranks of n floats at element offset off of a symmetric buffer (bufs_dev: device array of the N base
- * pointers).  mode 0 one-shot -> out (local); mode 1 two-shot, in place in every rank's buffer (+ copy to out). */
-int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, int off, int n, float* out, int mode, void* ctrl,
-                      void* stream);
+ * pointers).  mode 0 one-shot -> out (local); mode 1 two-shot, in place in every rank's buffer (+ copy to out).
+ * mc_buf: NVLS multicast address of the same buffer or NULL; when set, mode 0 reads every element with one in-switch
+ * reduction and mode 1 reduces its shard in the switch and multicasts the sums back. */
+int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, float* mc_buf, int off, int n, float* out, int mode,
+                      void* ctrl, void* stream);
 int dtm_broadcast_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, int off, int n, int root, void* ctrl, void* stream);
 
 #ifdef __cplusplus

@@ -60,7 +60,9 @@ def main() -> int:
     from distributed_tensorflow_ibm_mnist_b200.train.native_engine import NativeEngine
 
     comm = PeerComm(dist.group.WORLD, dev)
-    report: dict = {"world": world, "checks": {}, "sweep": []}
+    report: dict = {"world": world, "nvls": comm.nvls, "checks": {}, "sweep": []}
+    if rank == 0:
+        print(f"[info] world={world} nvls_multicast={comm.nvls}", flush=True)
     ok = True
 
     def check(name: str, cond: bool, info=None):
@@ -86,11 +88,21 @@ def main() -> int:
         for p in parts[1:]:
             fixed += p
         for mode in ("one_shot", "two_shot"):
-            got = comm.all_reduce(x, mode)
+            got = comm.all_reduce(x, mode, nvls=False)
             torch.cuda.synchronize()
             check(f"allreduce_{mode}_{n}_vs_nccl", torch.allclose(got, want, rtol=1e-5, atol=1e-5),
                   float((got - want).abs().max()))
             check(f"allreduce_{mode}_{n}_bit_exact_fixed_order", torch.equal(got, fixed))
+            if comm.nvls:
+                # in-switch reduction: the summation order is the switch's, so compare numerically and require that
+                # every rank holds the same bits
+                got = comm.all_reduce(x, mode, nvls=True)
+                torch.cuda.synchronize()
+                check(f"allreduce_nvls_{mode}_{n}_vs_nccl", torch.allclose(got, want, rtol=1e-5, atol=1e-5),
+                      float((got - want).abs().max()))
+                g0 = got.clone()
+                dist.broadcast(g0, src=0)
+                check(f"allreduce_nvls_{mode}_{n}_ranks_agree_bitwise", torch.equal(g0, got))
 
     # ---- fused all-reduce + update vs NCCL + single-GPU update --------------------------------------------
     for kind in ("sgd", "momentum", "adam"):
@@ -206,12 +218,14 @@ def main() -> int:
             out = torch.empty(n, device=dev)
             iters = 50 if size <= (1 << 22) else 10
             row = {"bytes": size}
-            for mode in ("one_shot", "two_shot"):
-                if mode == "one_shot" and size > (64 << 20):
-                    continue
-                ms = timed(lambda: comm.all_reduce_inplace(buf, n, out, mode), dev, iters)
-                row[mode + "_us"] = ms * 1e3
-                row[mode + "_busbw_GBs"] = 2 * (world - 1) / world * size / (ms * 1e-3) / 1e9
+            variants = [("", False)] + ([("nvls_", True)] if comm.nvls else [])
+            for prefix, use_mc in variants:
+                for mode in ("one_shot", "two_shot"):
+                    if mode == "one_shot" and size > (64 << 20):
+                        continue
+                    ms = timed(lambda: comm.all_reduce_inplace(buf, n, out, mode, use_mc), dev, iters)
+                    row[prefix + mode + "_us"] = ms * 1e3
+                    row[prefix + mode + "_busbw_GBs"] = 2 * (world - 1) / world * size / (ms * 1e-3) / 1e9
             ms = timed(lambda: dist.all_reduce(x), dev, iters)
             row["nccl_us"] = ms * 1e3
             row["nccl_busbw_GBs"] = 2 * (world - 1) / world * size / (ms * 1e-3) / 1e9
@@ -219,22 +233,41 @@ def main() -> int:
             if rank == 0:
                 print("[sweep] " + json.dumps(row), flush=True)
             size *= 4
-        # the fused gradient exchange of the two model sizes: time per call and fraction of the NVLink roofline
+        # the fused gradient exchange of the two model sizes: time per call and fraction of the NVLink roofline.
+        #   canonical roofline  = 2 (N-1)/N S / 900 GB/s: what a two-shot fp32 all-reduce has to move per direction
+        #                         (BASELINE.md section 3);
+        #   own-bytes roofline  = the bytes THIS kernel moves in its busier direction / 900 GB/s (bf16-only all-gather of
+        #                         the tensor-core-only variables; in-switch reduction when NVLS is on).
+        LINK = 900e9
         for preset in ("baseline", "wide"):
-            spec = presets.make_spec(preset)
-            comm.ctx = None
-            flat = FlatParams(spec, device=dev, allocator=comm.flat_allocator())
-            cfg = flat.update_config(optimizer="adam", base_lr=1e-3)
-            st = native.new_state(dev)
-            native.state_init(st)
-            ms = timed(lambda: comm.fused_allreduce_update(cfg, st, flat, 0, flat.total, finish=True), dev, 20)
-            link_bytes = (world - 1) / world * flat.total * 4          # per direction: gradients in, weights out
-            roof_us = link_bytes / 770e9 * 1e6                          # measured peer-copy bandwidth (B200_PROFILING.md)
-            row = {"fused_allreduce_adam": preset, "elements": flat.total, "us": ms * 1e3, "link_bytes_per_dir": link_bytes,
-                   "nvlink_roofline_us_at_770GBs": roof_us, "fraction_of_roofline": roof_us / (ms * 1e3)}
-            report["sweep"].append(row)
-            if rank == 0:
-                print("[sweep] " + json.dumps(row), flush=True)
+            for use_mc in ([False, True] if comm.nvls else [False]):
+                spec = presets.make_spec(preset)
+                comm.ctx = None
+                comm.use_multicast = use_mc
+                flat = FlatParams(spec, device=dev, allocator=comm.flat_allocator())
+                cfg = flat.update_config(optimizer="adam", base_lr=1e-3)
+                st = native.new_state(dev)
+                native.state_init(st)
+                ms = timed(lambda: comm.fused_allreduce_update(cfg, st, flat, 0, flat.total, finish=True), dev, 20)
+                S = flat.total * 4.0
+                gather = sum((2.0 if cfg.seg_gather_bf16[i] else 4.0) * (cfg.seg_offset[i + 1] - cfg.seg_offset[i])
+                             for i in range(cfg.n_segments))
+                f = (world - 1) / world
+                if use_mc:
+                    out_b, in_b = S + gather / world, S / world + f * gather
+                else:
+                    out_b = in_b = f * (S + gather)
+                own = max(out_b, in_b)
+                row = {"fused_allreduce_adam": preset, "nvls": use_mc, "elements": flat.total, "us": ms * 1e3,
+                       "canonical_link_bytes_per_dir": 2 * f * S, "canonical_roofline_us": 2 * f * S / LINK * 1e6,
+                       "fraction_of_canonical_roofline": 2 * f * S / LINK * 1e6 / (ms * 1e3),
+                       "own_link_bytes_busier_dir": own, "own_roofline_us": own / LINK * 1e6,
+                       "fraction_of_own_roofline": own / LINK * 1e6 / (ms * 1e3),
+                       "effective_link_GBs": own / (ms * 1e-3) / 1e9}
+                report["sweep"].append(row)
+                if rank == 0:
+                    print("[sweep] " + json.dumps(row), flush=True)
+        comm.use_multicast = comm.nvls
 
     report["ok"] = ok
     if rank == 0:
