@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(512, 1)
 fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cfg, dtm_train_state* __restrict__ st,
                               int lo, int hi, float* __restrict__ slot0, float* __restrict__ slot1,
                               float* __restrict__ ema, __nv_bfloat16* __restrict__ w_bf16, CommCtrl* __restrict__ ctrl,
-                              int do_finish) {
+                              int do_finish, int depth) {
   const int N = ctx.world, r = ctx.rank;
   const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
   const UpdateScalars u = make_update_scalars(cfg, st, 1.0f / static_cast<float>(N));
@@ -242,16 +242,16 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   };
   const int step = nthreads * 4;
   if (nvls) {
-    // four in-switch reductions in flight per thread before the first one is consumed
-    constexpr int U = 4;
-    for (int base = s_lo + tid * 4; base < s_hi; base += step * U) {
+    // `depth` (<= 8) in-switch reductions in flight per thread before the first one is consumed
+    constexpr int U = 8;
+    for (int base = s_lo + tid * 4; base < s_hi; base += step * depth) {
       float4 g[U];
 #pragma unroll
       for (int k = 0; k < U; ++k)
-        if (base + k * step < s_hi) g[k] = mc_ld_reduce_v4(ctx.mc_grad + base + k * step);
+        if (k < depth && base + k * step < s_hi) g[k] = mc_ld_reduce_v4(ctx.mc_grad + base + k * step);
 #pragma unroll
       for (int k = 0; k < U; ++k)
-        if (base + k * step < s_hi) apply(base + k * step, g[k]);
+        if (k < depth && base + k * step < s_hi) apply(base + k * step, g[k]);
     }
   } else if (N == 8 || N == 4 || N == 2) {
     // two float4 per thread and iteration: 2(N-1) NVLink round trips overlap, and the second one hides the optimizer
@@ -408,6 +408,13 @@ static int comm_grid(size_t elems, int max_ctas = 0) {
   return static_cast<int>(want > static_cast<size_t>(cap) ? cap : want);
 }
 
+// in-flight multimem.ld_reduce per thread in the fused exchange (tuning knob, DTM_COMM_DEPTH=1..8)
+static int comm_depth() {
+  const char* e = getenv("DTM_COMM_DEPTH");   // read per launch (cheap) so that tools can sweep it inside one process
+  const int v = e ? atoi(e) : 2;   // 8-GPU sweep (profiles/fused_exchange_8gpu_sweep_r1.json): 1-2 best, 8 worst
+  return v < 1 ? 1 : (v > 8 ? 8 : v);
+}
+
 static int check_ctx(const dtm_peer_ctx* ctx) {
   if (!ctx) return dtm_fail("comm: null context");
   if (ctx->world < 1 || ctx->world > DTM_MAX_RANKS) return dtm_fail("comm: world size out of range");
@@ -461,7 +468,7 @@ extern "C" int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_upd
   if (cfg->optimizer == DTM_OPT_MOMENTUM && !slot0) return dtm_fail("fused_allreduce_update: Momentum needs slot0");
   return launch_cooperative(fused_allreduce_update_kernel, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
                             static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
-                            static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish);
+                            static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
 }
 
 extern "C" int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, float* mc_buf, int off, int n, float* out, int mode,
