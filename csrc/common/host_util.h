@@ -31,4 +31,26 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64
 
 int device_sm_count();
 
+// Programmatic dependent launch mode: 0 off (every kernel starts after its predecessor has drained), 1 strict, 2 early
+// weights (see runtime.cu).  DTM_PDL=0|1|2 in the environment, or dtm_set_pdl_mode().
+int pdl_mode();
+bool pdl_enabled();
+
+// Launch with the programmatic-stream-serialization attribute: the kernel may begin its prologue while the previous
+// kernel of the stream is finishing; the kernel itself calls pdl_wait() (ptx.cuh) before it touches that kernel's output.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 }  // namespace dtm

@@ -21,6 +21,16 @@ DTM_DEVICE uint32_t lane_id() {
   return l;
 }
 
+// Programmatic dependent launch (PDL).  A kernel launched with the programmatic-stream-serialization attribute may start
+// while its predecessor in the stream is still running; everything it does before pdl_wait() must be independent of the
+// predecessor's output (barrier init, TMEM allocation, staging of weights that were written at least two kernels
+// upstream).  pdl_wait() returns once the predecessor grid has completed and its memory is visible; without the launch
+// attribute it returns immediately.  EVERY thread of EVERY kernel in a PDL chain calls it, so that "grid complete"
+// stays transitive along the chain.  pdl_launch_dependents() lets the next kernel's CTAs be scheduled as soon as SM
+// resources free up.
+DTM_DEVICE void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+DTM_DEVICE void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 DTM_DEVICE bool elect_one() {
   uint32_t pred = 0;
   asm volatile(

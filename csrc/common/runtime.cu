@@ -1,4 +1,5 @@
 // Runtime glue of libdtm_b200: error strings, device queries, TMA tensor-map construction.
+#include <stdlib.h>
 #include "host_util.h"
 #include "../../include/dtm_b200.h"
 #include <mutex>
@@ -72,7 +73,25 @@ int device_sm_count() {
   return cached[dev];
 }
 
+// 0 = off, 1 = strict (a kernel reads nothing from global memory before its dependency wait), 2 = early weights (kernels
+// may stage WEIGHTS before the wait; only valid when the caller knows that no weight is written by the kernel launched
+// immediately before - true for the training engine's schedule, which opts in around its own launches).
+static int g_pdl_mode = -1;
+int pdl_mode() {
+  if (g_pdl_mode >= 0) return g_pdl_mode;
+  const char* e = getenv("DTM_PDL");   // read per launch: a graph capture bakes the choice in, tools can A/B in one process
+  if (!e) return 1;
+  return e[0] == '0' ? 0 : (e[0] == '2' ? 2 : 1);
+}
+bool pdl_enabled() { return pdl_mode() != 0; }
+
 }  // namespace dtm
+
+extern "C" int dtm_set_pdl_mode(int mode) {
+  const int prev = dtm::g_pdl_mode;
+  dtm::g_pdl_mode = mode < 0 ? -1 : (mode > 2 ? 2 : mode);
+  return prev;
+}
 
 extern "C" const char* dtm_last_error(void) { return dtm::g_last_error; }
 

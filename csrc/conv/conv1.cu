@@ -58,6 +58,8 @@ conv1_wgrad_kernel(const void* __restrict__ x, int in_is_float, const __nv_bfloa
 #pragma unroll
   for (int t = 0; t < 25 * CIN; ++t) acc[t] = 0.0f;
   float accb = 0.0f;
+  pdl_wait();
+  pdl_launch_dependents();
 
   for (int img = blockIdx.x; img < batch; img += gridDim.x) {
     __syncthreads();
@@ -111,8 +113,8 @@ extern "C" int dtm_conv1_wgrad(const void* x, int in_is_float, int channels, con
   const int grid = min(batch, 4 * device_sm_count());   // 3-4 CTAs per SM: the loop is LDS/FMA latency bound
   const __nv_bfloat16* g = static_cast<const __nv_bfloat16*>(grad_pooled);
   const uint8_t* a = static_cast<const uint8_t*>(argmax);
-  if (channels == 1) conv1_wgrad_kernel<1><<<grid, 256, 0, s>>>(x, in_is_float, g, a, batch, dw, db);
-  else               conv1_wgrad_kernel<3><<<grid, 256, 0, s>>>(x, in_is_float, g, a, batch, dw, db);
+  if (channels == 1) DTM_CUDA_OK(launch_pdl(conv1_wgrad_kernel<1>, dim3(grid), dim3(256), 0, s, x, in_is_float, g, a, batch, dw, db));
+  else               DTM_CUDA_OK(launch_pdl(conv1_wgrad_kernel<3>, dim3(grid), dim3(256), 0, s, x, in_is_float, g, a, batch, dw, db));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -71,6 +71,11 @@ conv1_tc_kernel(const void* __restrict__ x, int in_is_float, const float* __rest
     fence_mbar_init();
   }
   if (warp == 9) { tmem_alloc(&tmem_slot, T1_ACC * 4 * T1_OUT); tmem_relinquish(); }
+  for (int i = threadIdx.x; i < 2 * CIN * T1_PITCH * T1_PITCH; i += blockDim.x) s_img[i] = __float2bfloat16(0.0f);
+  // conv1 opens the step: its predecessor in the stream is the previous step's update kernel, which writes these very
+  // weights - so the dependency wait comes before the first global read
+  pdl_wait();
+  pdl_launch_dependents();
   if (threadIdx.x < T1_OUT) s_bias[threadIdx.x] = bias[threadIdx.x];
   // filter: TF layout [tap][ci][co] fp32 -> B[k = tap*CIN + ci][n = co] as [k/8][n][k%8] bf16, zero for k >= K
   for (int i = threadIdx.x; i < G::K8 * T1_OUT * 8; i += blockDim.x) {
@@ -79,7 +84,6 @@ conv1_tc_kernel(const void* __restrict__ x, int in_is_float, const float* __rest
     const float v = k < G::K ? w[k * T1_OUT + n] : 0.0f;
     reinterpret_cast<__nv_bfloat16*>(s_b)[i] = __float2bfloat16(v);
   }
-  for (int i = threadIdx.x; i < 2 * CIN * T1_PITCH * T1_PITCH; i += blockDim.x) s_img[i] = __float2bfloat16(0.0f);
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
@@ -273,11 +277,11 @@ extern "C" int dtm_conv1_fwd(const void* x, int in_is_float, int channels, const
   const int per_sm = channels == 1 ? 2 : 1;
   const int grid = min(batch, per_sm * device_sm_count());
   if (channels == 1) {
-    if (lrn) conv1_tc_kernel<1, true><<<grid, 320, T1Geom<1>::SMEM, s>>>(x, in_is_float, w, bias, batch, p, a, r);
-    else     conv1_tc_kernel<1, false><<<grid, 320, T1Geom<1>::SMEM, s>>>(x, in_is_float, w, bias, batch, p, a, r);
+    if (lrn) DTM_CUDA_OK(launch_pdl(conv1_tc_kernel<1, true>, dim3(grid), dim3(320), T1Geom<1>::SMEM, s, x, in_is_float, w, bias, batch, p, a, r));
+    else     DTM_CUDA_OK(launch_pdl(conv1_tc_kernel<1, false>, dim3(grid), dim3(320), T1Geom<1>::SMEM, s, x, in_is_float, w, bias, batch, p, a, r));
   } else {
-    if (lrn) conv1_tc_kernel<3, true><<<grid, 320, T1Geom<3>::SMEM, s>>>(x, in_is_float, w, bias, batch, p, a, r);
-    else     conv1_tc_kernel<3, false><<<grid, 320, T1Geom<3>::SMEM, s>>>(x, in_is_float, w, bias, batch, p, a, r);
+    if (lrn) DTM_CUDA_OK(launch_pdl(conv1_tc_kernel<3, true>, dim3(grid), dim3(320), T1Geom<3>::SMEM, s, x, in_is_float, w, bias, batch, p, a, r));
+    else     DTM_CUDA_OK(launch_pdl(conv1_tc_kernel<3, false>, dim3(grid), dim3(320), T1Geom<3>::SMEM, s, x, in_is_float, w, bias, batch, p, a, r));
   }
   DTM_CUDA_OK(cudaGetLastError());
   return 0;

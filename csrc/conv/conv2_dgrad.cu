@@ -30,7 +30,7 @@ template <bool LRN>
 __global__ void __launch_bounds__(128 + 32 * DgEpi<LRN>::WARPS, 1)
 conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* __restrict__ w2,
                    const uint8_t* __restrict__ w_packed, const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ pool_raw, int batch,
-                   __nv_bfloat16* __restrict__ dpool1) {
+                   __nv_bfloat16* __restrict__ dpool1, int early_weights) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t img_full[DG_BUFS], img_empty[DG_BUFS], acc_full[2], acc_empty[2], w_full;
   __shared__ uint32_t tmem_slot;
@@ -43,11 +43,16 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
 
+  if (!early_weights) pdl_wait();   // strict mode: nothing is read from global memory before the dependency wait
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < DG_BUFS; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 32 * DgEpi<LRN>::WARPS); }
     mbar_init(&w_full, 1);
     fence_mbar_init();
+    if (w_packed != nullptr) {   // written by the previous step's update kernel: fetch before the dependency wait
+      mbar_arrive_expect_tx(&w_full, DG_W_BYTES);
+      bulk_load_1d(s_w, w_packed, DG_W_BYTES, &w_full);
+    }
   }
   if (warp == 2) { tmem_alloc(&tmem_slot, 128); tmem_relinquish(); }
   {
@@ -67,13 +72,11 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   const int first = blockIdx.x, stride = gridDim.x;
+  pdl_wait();                 // the unpooled gradient planes (and everything upstream) are complete from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (elect_one()) {
-      if (w_packed != nullptr) {
-        mbar_arrive_expect_tx(&w_full, DG_W_BYTES);
-        bulk_load_1d(s_w, w_packed, DG_W_BYTES, &w_full);
-      }
       int it = 0;
       for (int img = first; img < batch; img += stride, ++it) {
         const int b = it % DG_BUFS;
@@ -222,13 +225,14 @@ extern "C" int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, cons
     configured = true;
   }
   const int grid = min(batch, device_sm_count());
-  auto launch = [&](auto kern) {
-    kern<<<grid, lrn ? 256 : 384, DG_SMEM, s>>>(static_cast<const uint8_t*>(dz2_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
-                                    static_cast<const uint8_t*>(packed), static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(pool_raw), batch,
-                                    static_cast<__nv_bfloat16*>(dpool1));
+  auto launch = [&](auto kern) -> int {
+    DTM_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(lrn ? 256 : 384), DG_SMEM, s, static_cast<const uint8_t*>(dz2_planes),
+                           static_cast<const __nv_bfloat16*>(w2_bf16), static_cast<const uint8_t*>(packed),
+                           static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(pool_raw), batch,
+                           static_cast<__nv_bfloat16*>(dpool1), pdl_mode() == 2 ? 1 : 0));
+    return 0;
   };
-  if (lrn) launch(conv2_dgrad_kernel<true>);
-  else     launch(conv2_dgrad_kernel<false>);
+  if (int rc = lrn ? launch(conv2_dgrad_kernel<true>) : launch(conv2_dgrad_kernel<false>)) return rc;
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -38,7 +38,8 @@ template <bool LRN> struct C2Epi { static constexpr int WARPS = LRN ? 4 : 8; sta
 template <bool LRN>
 __global__ void __launch_bounds__(128 + 32 * C2Epi<LRN>::WARPS, 1)
 conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ w2,
-                 const uint8_t* __restrict__ w_packed, const float* __restrict__ bias, int batch, __nv_bfloat16* __restrict__ p2, uint8_t* __restrict__ argmax, __nv_bfloat16* __restrict__ act2) {
+                 const uint8_t* __restrict__ w_packed, const float* __restrict__ bias, int batch, __nv_bfloat16* __restrict__ p2, uint8_t* __restrict__ argmax, __nv_bfloat16* __restrict__ act2,
+                 int early_weights) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t img_full[C2_BUFS], img_empty[C2_BUFS], acc_full[2], acc_empty[2], w_full;
   __shared__ uint32_t tmem_slot;
@@ -53,11 +54,18 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
   const uint32_t lane = lane_id();
 
   // ---- one-time setup -------------------------------------------------------------------------
+  if (!early_weights) pdl_wait();   // strict mode: nothing is read from global memory before the dependency wait
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < C2_BUFS; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 32 * C2Epi<LRN>::WARPS); }
     mbar_init(&w_full, 1);
     fence_mbar_init();
+    // early-weights mode: the packed filter image was written by the previous step's update kernel, so this 100 KiB
+    // copy (and the bias / self-pack reads below) may overlap the tail of the preceding kernel
+    if (w_packed != nullptr) {
+      mbar_arrive_expect_tx(&w_full, C2_W_BYTES);
+      bulk_load_1d(s_w, w_packed, C2_W_BYTES, &w_full);
+    }
   }
   if (warp == 2) { tmem_alloc(&tmem_slot, 256); tmem_relinquish(); }
   if (threadIdx.x < C2_OUT) s_bias[threadIdx.x] = bias[threadIdx.x];
@@ -84,6 +92,8 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  pdl_wait();                 // conv1's planes are complete and visible from here on
+  pdl_launch_dependents();
 
   const int first = blockIdx.x;
   const int stride = gridDim.x;
@@ -91,10 +101,6 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
   if (warp == 0) {
     // ---- producer: one 16 KiB bulk copy per image ------------------------------------------------
     if (elect_one()) {
-      if (w_packed != nullptr) {
-        mbar_arrive_expect_tx(&w_full, C2_W_BYTES);
-        bulk_load_1d(s_w, w_packed, C2_W_BYTES, &w_full);
-      }
       int it = 0;
       for (int img = first; img < batch; img += stride, ++it) {
         const int b = it % C2_BUFS;
@@ -245,13 +251,13 @@ extern "C" int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const v
     configured = true;
   }
   const int grid = min(batch, device_sm_count());
-  auto args = [&](auto kern) {
-    kern<<<grid, lrn ? 256 : 384, C2_SMEM, s>>>(static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
+  auto args = [&](auto kern) -> int {
+    DTM_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(lrn ? 256 : 384), C2_SMEM, s, static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
                                     static_cast<const uint8_t*>(packed), bias, batch, static_cast<__nv_bfloat16*>(p2), static_cast<uint8_t*>(argmax),
-                                    static_cast<__nv_bfloat16*>(act2));
+                                    static_cast<__nv_bfloat16*>(act2), pdl_mode() == 2 ? 1 : 0));
+    return 0;
   };
-  if (lrn) args(conv2_fwd_kernel<true>);
-  else     args(conv2_fwd_kernel<false>);
+  if (int rc = lrn ? args(conv2_fwd_kernel<true>) : args(conv2_fwd_kernel<false>)) return rc;
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

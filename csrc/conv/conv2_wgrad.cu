@@ -83,6 +83,8 @@ conv2_wgrad_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __restr
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   const int first = blockIdx.x, stride = gridDim.x;
+  pdl_wait();                 // both operand plane sets come from preceding kernels
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -149,6 +151,8 @@ extern "C" int dtm_conv2_wgrad(const void* p1_planes, const void* dz2_planes, in
     configured = true;
   }
   const int gx = min(batch, max(1, device_sm_count() / 2));
+  // plain launch: in the training schedule this kernel joins two streams (dgrad's and the side stream's own history); a
+  // programmatic edge is only defined towards a single predecessor
   conv2_wgrad_kernel<<<dim3(gx, 2), 256, WG_SMEM, s>>>(static_cast<const uint8_t*>(p1_planes),
                                                       static_cast<const uint8_t*>(dz2_planes), batch, dw2);
   DTM_CUDA_OK(cudaGetLastError());

@@ -17,6 +17,8 @@ __global__ void __launch_bounds__(256)
 unpool2_kernel(const __nv_bfloat16* __restrict__ dp2, const uint8_t* __restrict__ argmax, int batch,
                uint8_t* __restrict__ dz2_planes, float* __restrict__ db2) {
   __shared__ float s_db[32][UP_C + 1];
+  pdl_wait();
+  pdl_launch_dependents();
   const int c8 = threadIdx.x & 7;
   const int r = threadIdx.x >> 3;
   float part[8];
@@ -66,6 +68,8 @@ unpool2_lrn_kernel(const __nv_bfloat16* __restrict__ dp2, const uint8_t* __restr
   __shared__ float s_db[UP_C];
   if (threadIdx.x < UP_C) s_db[threadIdx.x] = 0.0f;
   __syncthreads();
+  pdl_wait();
+  pdl_launch_dependents();
   const int pix = blockIdx.x * blockDim.x + threadIdx.x;
   const bool active = pix < batch * IMG * IMG;
   float g[UP_C];
@@ -140,6 +144,8 @@ colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, int M, int N, float* __r
   const int n = blockIdx.x * 32 + (threadIdx.x & 31);
   const int r = threadIdx.x >> 5;
   __shared__ float s[8][33];
+  pdl_wait();
+  pdl_launch_dependents();
   float acc = 0.0f;
   if (n < N)
     for (int m = blockIdx.y * 8 + r; m < M; m += gridDim.y * 8) acc += __bfloat162float(x[static_cast<size_t>(m) * N + n]);
@@ -163,15 +169,14 @@ extern "C" int dtm_unpool2(const void* dp2, const void* argmax, const void* act2
   if (lrn) {
     if (!act2) return dtm_fail("unpool2: LRN backward needs act2");
     const int pixels = batch * IMG * IMG;
-    unpool2_lrn_kernel<<<(pixels + 127) / 128, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(dp2),
-                                                           static_cast<const uint8_t*>(argmax),
-                                                           static_cast<const __nv_bfloat16*>(act2), batch,
-                                                           static_cast<uint8_t*>(dz2_planes), db2);
+    DTM_CUDA_OK(launch_pdl(unpool2_lrn_kernel, dim3((pixels + 127) / 128), dim3(128), 0, s, static_cast<const __nv_bfloat16*>(dp2),
+                           static_cast<const uint8_t*>(argmax), static_cast<const __nv_bfloat16*>(act2), batch,
+                           static_cast<uint8_t*>(dz2_planes), db2));
   } else {
     const int rows = batch * 49;
     const int grid = min((rows + 31) / 32, 4 * device_sm_count());
-    unpool2_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dp2), static_cast<const uint8_t*>(argmax), batch,
-                                        static_cast<uint8_t*>(dz2_planes), db2);
+    DTM_CUDA_OK(launch_pdl(unpool2_kernel, dim3(grid), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(dp2),
+                           static_cast<const uint8_t*>(argmax), batch, static_cast<uint8_t*>(dz2_planes), db2));
   }
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
@@ -182,7 +187,7 @@ extern "C" int dtm_colsum_bf16(const void* x, int M, int N, float* out, void* st
   if (M <= 0 || N <= 0) return dtm_fail("colsum: M and N must be positive");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   dim3 grid((N + 31) / 32, min(32, (M + 7) / 8));
-  colsum_bf16_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), M, N, out);
+  DTM_CUDA_OK(launch_pdl(colsum_bf16_kernel, grid, dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), M, N, out));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -84,6 +84,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_d = tmem_slot;
+  pdl_wait();                 // operands produced by the preceding kernel are complete from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
@@ -237,7 +239,7 @@ static int launch_gemm_s(const CUtensorMap& ta, const CUtensorMap& tb, const Gem
     DTM_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(STAGES)));
     configured = true;
   }
-  kern<<<grid, 256, gemm_smem_bytes(STAGES), s>>>(ta, tb, g);
+  DTM_CUDA_OK(launch_pdl(kern, grid, dim3(256), gemm_smem_bytes(STAGES), s, ta, tb, g));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

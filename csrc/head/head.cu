@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(256)
 head_forward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, const float* __restrict__ w,
                     const float* __restrict__ bias, const int* __restrict__ labels, float grad_scale, float loss_scale,
                     float* __restrict__ logits_out, float* __restrict__ probs_out, float* __restrict__ dlogits,
-                    dtm_train_state* __restrict__ state) {
+                    dtm_train_state* __restrict__ state, int early_weights) {
   __shared__ float s_w[HF_CHUNK * HF_PITCH];   // 44 KiB: the weight rows of the current chunk, shared by the CTA's 8 rows
   __shared__ float s_loss[8], s_corr[8];
   __shared__ unsigned int s_nan;
@@ -32,6 +32,7 @@ head_forward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, 
   const uint32_t lane = lane_id();
   const bool row_ok = row < batch;
   if (threadIdx.x == 0) s_nan = 0;
+  if (!early_weights) pdl_wait();   // strict mode: nothing is read from global memory before the dependency wait
   float acc[NCLS];
 #pragma unroll
   for (int c = 0; c < NCLS; ++c) acc[c] = 0.0f;
@@ -56,6 +57,7 @@ head_forward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, 
         s_w[(idx / NCLS) * HF_PITCH + idx % NCLS] = w[static_cast<size_t>(k0) * NCLS + idx];
     }
     __syncthreads();
+    if (k0 == 0) { pdl_wait(); pdl_launch_dependents(); }   // the weights above are older than the preceding kernel; h is not
     if (row_ok) {
 #pragma unroll 8
       for (int k = lane; k < kc; k += 32) {
@@ -128,6 +130,8 @@ head_backward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden,
   const int r = threadIdx.x >> 5;
   const int k = blockIdx.x * HB_COLS + kk;
   const bool col_ok = k < hidden;
+  pdl_wait();                 // dlogits / h come from the preceding kernels
+  pdl_launch_dependents();
   float wk[NCLS];
 #pragma unroll
   for (int c = 0; c < NCLS; ++c) wk[c] = col_ok ? w[static_cast<size_t>(k) * NCLS + c] : 0.0f;
@@ -180,8 +184,8 @@ extern "C" int dtm_head_forward(const void* h, int batch, int hidden, const floa
   using namespace dtm;
   if (batch <= 0 || hidden <= 0) return dtm_fail("head_forward: batch and hidden must be positive");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  head_forward_kernel<<<(batch + 7) / 8, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(h), batch, hidden, w, bias, labels,
-                                                     grad_scale, loss_scale, logits, probs, dlogits, state);
+  DTM_CUDA_OK(launch_pdl(head_forward_kernel, dim3((batch + 7) / 8), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(h), batch, hidden,
+                         w, bias, labels, grad_scale, loss_scale, logits, probs, dlogits, state, pdl_mode() == 2 ? 1 : 0));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -194,8 +198,8 @@ extern "C" int dtm_head_backward(const void* h, int batch, int hidden, const flo
   const int col_blocks = (hidden + HB_COLS - 1) / HB_COLS;
   int split = 1;
   while (col_blocks * split < 2 * device_sm_count() && split * 16 <= batch && split < 16) split *= 2;
-  head_backward_kernel<<<dim3(col_blocks, split), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(h), batch, hidden, w, dlogits,
-                                                              inv_keep, static_cast<__nv_bfloat16*>(dh), dw, db_out, db_hidden);
+  DTM_CUDA_OK(launch_pdl(head_backward_kernel, dim3(col_blocks, split), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(h), batch,
+                         hidden, w, dlogits, inv_keep, static_cast<__nv_bfloat16*>(dh), dw, db_out, db_hidden));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

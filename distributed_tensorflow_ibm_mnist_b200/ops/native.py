@@ -26,6 +26,7 @@ _lib.register("dtm_conv2_pack_weights", [P, P, P, P])
 _lib.register("dtm_conv2_wgrad", [P, P, I, P, P])
 _lib.register("dtm_unpool2", [P, P, P, I, I, P, P, P])
 _lib.register("dtm_colsum_bf16", [P, I, I, P, P])
+_lib.register("dtm_set_pdl_mode", [I])
 _lib.register("dtm_head_forward", [P, I, I, P, P, P, F, F, P, P, P, P, P])
 _lib.register("dtm_head_backward", [P, I, I, P, P, F, P, P, P, P, P])
 _lib.register("dtm_fused_update", [P, P, P, P, P, P, P, P, F, P])
@@ -121,6 +122,27 @@ def unpool2(dp2, argmax, act2, dz2_planes, db2, *, batch, lrn=False):
 def colsum_bf16(x, out):
     M, N = x.shape
     check(_L().dtm_colsum_bf16(ptr(x), M, N, ptr(out), current_stream()), "colsum_bf16")
+
+
+class pdl_mode:
+    """``with pdl_mode(2):`` — programmatic-dependent-launch mode for the launches inside the block (0 off, 1 strict,
+    2 early weights; see ``dtm_set_pdl_mode``).  The ``DTM_PDL`` environment variable, when set, wins: it is the A/B
+    switch of the tools."""
+
+    def __init__(self, mode: int):
+        self.mode = mode
+        self.prev = None
+
+    def __enter__(self):
+        import os
+        if os.environ.get("DTM_PDL") is None:
+            self.prev = _L().dtm_set_pdl_mode(int(self.mode))
+        return self
+
+    def __exit__(self, *exc):
+        if self.prev is not None:
+            _L().dtm_set_pdl_mode(int(self.prev))
+        return False
 
 
 def head_forward(h, w, bias, labels, *, grad_scale, loss_scale, logits=None, probs=None, dlogits=None, state=None):

@@ -168,6 +168,12 @@ class NativeEngine:
 
     # ---- the kernel sequence ----------------------------------------------------------------------------
     def _forward(self, x, labels, *, training: bool, state, count=None) -> None:
+        # early-weights PDL mode: in this schedule no kernel that stages weights before its dependency wait (conv2_fwd,
+        # conv2_dgrad, head_forward) directly follows a kernel that writes weights
+        with native.pdl_mode(2):
+            self._forward_impl(x, labels, training=training, state=state, count=count)
+
+    def _forward_impl(self, x, labels, *, training: bool, state, count=None) -> None:
         s, f, B = self.spec, self.flat, self.B
         n = 0
         self._mark("start")
@@ -199,6 +205,10 @@ class NativeEngine:
             count[0] += n
 
     def _backward(self, x, count, with_comm: bool = True) -> None:
+        with native.pdl_mode(2):
+            self._backward_impl(x, count, with_comm)
+
+    def _backward_impl(self, x, count, with_comm: bool = True) -> None:
         s, f, B = self.spec, self.flat, self.B
         n = 0
         h = self.h2 if s.fc2 else self.h1

@@ -96,6 +96,12 @@ typedef struct dtm_peer_ctx {
 const char* dtm_last_error(void);
 int dtm_abi_version(void);
 int dtm_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin);
+/* Programmatic dependent launch (kernel prologues overlap the tail of the preceding kernel of the stream).
+ * 0 = off; 1 = strict: no kernel reads global memory before its dependency wait (default; always safe);
+ * 2 = early weights: conv2 / head kernels stage their WEIGHT operands before the wait - only valid if no weight buffer is
+ * written by the kernel launched immediately before them (the training engine's schedule; it switches to 2 around its own
+ * launches).  -1 = back to the DTM_PDL environment variable.  Process-wide, host-side; returns the previous setting. */
+int dtm_set_pdl_mode(int mode);
 
 /* ---- tcgen05 probe (tools/umma_probe.py) -------------------------------------------------------- */
 /* Copies `image` into shared memory, issues the listed tcgen05.mma ops, dumps 128 TMEM lanes x ncols.
