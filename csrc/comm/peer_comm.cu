@@ -294,14 +294,13 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   __shared__ unsigned int s_last;
   if (threadIdx.x == 0) s_last = (atomicAdd(&ctrl->ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
   __syncthreads();
-  if (s_last && threadIdx.x == 0) {
+  if (s_last) {   // the whole CTA: finish_step spreads the bookkeeping over its threads
     __threadfence();
-    ctrl->ticket = 0;
-    st_release_gpu(&ctrl->epoch, e0 + 2);
-    if (do_finish) {
-      const float lr_plain = cfg.base_lr * powf(cfg.decay_rate, cfg.decay_steps > 0 ? floorf((float)(st->global_step / cfg.decay_steps)) : 0.f);
-      finish_step(cfg, st, lr_plain);
+    if (threadIdx.x == 0) {
+      ctrl->ticket = 0;
+      st_release_gpu(&ctrl->epoch, e0 + 2);
     }
+    if (do_finish) finish_step(cfg, st, u.lr_plain);
   }
 }
 

@@ -19,7 +19,8 @@ constexpr int DG_CO = 64;                                // reduction channels p
 constexpr int DG_K = 25 * DG_CO;                         // 1600
 constexpr int DG_W_BYTES = DG_K * DG_CI * 2;             // 102400
 constexpr int DG_IMG_BYTES = plane_image_bytes(DG_CO);   // 32768
-constexpr int DG_BUFS = 2;
+constexpr int DG_BUFS = 3;
+constexpr int DG_ACC = 4;                                // TMEM accumulator ring: 4 x 32 columns
 constexpr int DG_SMEM = DG_W_BYTES + PL_GUARD_BYTES + DG_BUFS * DG_IMG_BYTES + PL_GUARD_BYTES + 128;
 
 // Like the forward kernel, the epilogue (TMEM read, activation fetch, mask, store) is a latency chain: without LRN two
@@ -32,7 +33,7 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
                    const uint8_t* __restrict__ w_packed, const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ pool_raw, int batch,
                    __nv_bfloat16* __restrict__ dpool1, int early_weights) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t img_full[DG_BUFS], img_empty[DG_BUFS], acc_full[2], acc_empty[2], w_full;
+  __shared__ uint64_t img_full[DG_BUFS], img_empty[DG_BUFS], acc_full[DG_ACC], acc_empty[DG_ACC], w_full;
   __shared__ uint32_t tmem_slot;
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -46,7 +47,7 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
   if (!early_weights) pdl_wait();   // strict mode: nothing is read from global memory before the dependency wait
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < DG_BUFS; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 32 * DgEpi<LRN>::WARPS); }
+    for (int i = 0; i < DG_ACC; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 32 * DgEpi<LRN>::WARPS); }
     mbar_init(&w_full, 1);
     fence_mbar_init();
     if (w_packed != nullptr) {   // written by the previous step's update kernel: fetch before the dependency wait
@@ -71,18 +72,20 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  // work unit = one M-tile (half an image), as in the forward kernel: 1024 units balance over 148 CTAs to 98.8 %
   const int first = blockIdx.x, stride = gridDim.x;
+  const int units = 2 * batch;
   pdl_wait();                 // the unpooled gradient planes (and everything upstream) are complete from here on
   pdl_launch_dependents();
 
   if (warp == 0) {
     if (elect_one()) {
       int it = 0;
-      for (int img = first; img < batch; img += stride, ++it) {
+      for (int u = first; u < units; u += stride, ++it) {
         const int b = it % DG_BUFS;
         mbar_wait(&img_empty[b], ((it / DG_BUFS) & 1) ^ 1, 20);
         mbar_arrive_expect_tx(&img_full[b], DG_IMG_BYTES);
-        bulk_load_1d(s_img + b * DG_IMG_BYTES, dz2_planes + static_cast<size_t>(img) * DG_IMG_BYTES, DG_IMG_BYTES, &img_full[b]);
+        bulk_load_1d(s_img + b * DG_IMG_BYTES, dz2_planes + static_cast<size_t>(u >> 1) * DG_IMG_BYTES, DG_IMG_BYTES, &img_full[b]);
       }
     }
   } else if (warp == 1) {
@@ -91,16 +94,16 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
       const UmmaDescBase w_desc = umma_desc_base(smem_u32(s_w), DG_CI * 16, 128, UMMA_SWIZZLE_NONE);
       if (w_packed != nullptr) mbar_wait(&w_full, 0, 24);
       int it = 0;
-      for (int img = first; img < batch; img += stride, ++it) {
+      for (int u = first; u < units; u += stride, ++it) {
         const int b = it % DG_BUFS;
-        const int a = it & 1;
-        mbar_wait(&acc_empty[a], ((it >> 1) & 1) ^ 1, 21);
+        const int a = it % DG_ACC;
+        mbar_wait(&acc_empty[a], ((it / DG_ACC) & 1) ^ 1, 21);
         mbar_wait(&img_full[b], (it / DG_BUFS) & 1, 22);
         tc_fence_after();
         const UmmaDescBase a_base = umma_desc_base(smem_u32(s_img + b * DG_IMG_BYTES), PL_PLANE_BYTES, 128, UMMA_SWIZZLE_NONE);
-#pragma unroll 1
-        for (int t = 0; t < 2; ++t) {
-          const uint32_t d_tmem = tmem_base + a * 64 + t * 32;
+        {
+          const int t = u & 1;
+          const uint32_t d_tmem = tmem_base + a * 32;
           const int tile_off = t * 128 * 16;
 #pragma unroll
           for (int tap = 0; tap < 25; ++tap) {
@@ -124,24 +127,25 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
     const int c0 = LRN ? 0 : static_cast<int>((warp - 4) >> 2) * 16;
     const int w_px = lane & 15, h_sub = lane >> 4;
     int it = 0;
-    for (int img = first; img < batch; img += stride, ++it) {
-      const int a = it & 1;
-      mbar_wait(&acc_full[a], (it >> 1) & 1, 23);
+    for (int u = first; u < units; u += stride, ++it) {
+      const int a = it % DG_ACC;
+      const int img = u >> 1;
+      mbar_wait(&acc_full[a], (it / DG_ACC) & 1, 23);
       tc_fence_after();
-#pragma unroll 1
-      for (int t = 0; t < 2; ++t) {
+      do {   // single pass; `continue` below leaves it for threads whose grid pixel is padding
+        const int t = u & 1;
         const int h = t * 8 + q * 2 + h_sub;
         const bool valid = h < IMG && w_px < IMG;
         float g[CH];
         if (LRN) {
           uint32_t r[32];
-          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 64 + t * 32, r);
+          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 32, r);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < CH; ++j) g[j] = __uint_as_float(r[j % 32]);
         } else {
           uint32_t r[16];
-          tmem_ld_x16(tmem_base + ((q * 32u) << 16) + a * 64 + t * 32 + c0, r);
+          tmem_ld_x16(tmem_base + ((q * 32u) << 16) + a * 32 + c0, r);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < CH; ++j) g[j] = __uint_as_float(r[j % 16]);
@@ -198,7 +202,7 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
           for (int i = 0; i < 8; ++i) o[i] = act[c8 * 8 + i] > 0.0f ? g[c8 * 8 + i] : 0.0f;
           dst[c8] = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
         }
-      }
+      } while (0);
       tc_fence_before();
       mbar_arrive(&acc_empty[a]);
     }
@@ -224,7 +228,7 @@ extern "C" int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, cons
     DTM_CUDA_OK(cudaFuncSetAttribute(conv2_dgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
     configured = true;
   }
-  const int grid = min(batch, device_sm_count());
+  const int grid = min(2 * batch, device_sm_count());
   auto launch = [&](auto kern) -> int {
     DTM_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(lrn ? 256 : 384), DG_SMEM, s, static_cast<const uint8_t*>(dz2_planes),
                            static_cast<const __nv_bfloat16*>(w2_bf16), static_cast<const uint8_t*>(packed),

@@ -4,8 +4,9 @@
 // Implicit GEMM without im2col.  The pooled conv1 activation arrives in the plane layout (plane_layout.cuh):
 // one cp.async.bulk drops a whole 16 KiB image into shared memory, and each of the 25 filter taps is the *same*
 // bytes seen through a UMMA descriptor whose start address is moved by (kh*16 + kw - 2) pixels.  Per image:
-//   2 M-tiles (image rows 0-7 / 8-15 of the 16-wide grid) x 25 taps x 2 K-chunks = 100 tcgen05.mma (128x64x16),
-// accumulating into a 128-column TMEM window that is double buffered against the epilogue.  The 100 KiB of
+//   2 M-tiles (image rows 0-7 / 8-15 of the 16-wide grid) x 25 taps x 2 K-chunks = 100 tcgen05.mma (128x64x16).
+// A work unit is ONE M-tile (finer load balance than whole images); its 64-column accumulator is one of a ring of four
+// in TMEM, so the MMA issuer runs up to three units ahead of the epilogue.  The 100 KiB of
 // filter weights are re-packed once per CTA into the canonical K-major operand layout and stay resident.
 //
 // Warp roles: 0 = bulk-copy producer, 1 = MMA issuer, 2 = TMEM allocator, 4-7 = epilogue (TMEM -> registers ->
@@ -22,7 +23,8 @@ constexpr int C2_OUT = 64;
 constexpr int C2_K = 25 * C2_IN;                       // 800
 constexpr int C2_W_BYTES = C2_K * C2_OUT * 2;          // 102400
 constexpr int C2_IMG_BYTES = plane_image_bytes(C2_IN); // 16384
-constexpr int C2_BUFS = 2;
+constexpr int C2_BUFS = 3;
+constexpr int C2_ACC = 4;                               // TMEM accumulator ring: 4 x 64 columns
 constexpr int C2_SMEM = C2_W_BYTES + PL_GUARD_BYTES + C2_BUFS * C2_IMG_BYTES + PL_GUARD_BYTES + 128;
 
 constexpr float LRN2_BIAS = 1.0f;
@@ -41,7 +43,7 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
                  const uint8_t* __restrict__ w_packed, const float* __restrict__ bias, int batch, __nv_bfloat16* __restrict__ p2, uint8_t* __restrict__ argmax, __nv_bfloat16* __restrict__ act2,
                  int early_weights) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t img_full[C2_BUFS], img_empty[C2_BUFS], acc_full[2], acc_empty[2], w_full;
+  __shared__ uint64_t img_full[C2_BUFS], img_empty[C2_BUFS], acc_full[C2_ACC], acc_empty[C2_ACC], w_full;
   __shared__ uint32_t tmem_slot;
   __shared__ float s_bias[C2_OUT];
 
@@ -57,7 +59,7 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
   if (!early_weights) pdl_wait();   // strict mode: nothing is read from global memory before the dependency wait
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < C2_BUFS; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 32 * C2Epi<LRN>::WARPS); }
+    for (int i = 0; i < C2_ACC; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 32 * C2Epi<LRN>::WARPS); }
     mbar_init(&w_full, 1);
     fence_mbar_init();
     // early-weights mode: the packed filter image was written by the previous step's update kernel, so this 100 KiB
@@ -95,18 +97,21 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
   pdl_wait();                 // conv1's planes are complete and visible from here on
   pdl_launch_dependents();
 
+  // work unit = one M-tile (half an image: grid rows 0-7 or 8-15).  1024 units over 148 CTAs balance to 98.8 %; whole
+  // images (3.46 per CTA) left the last of four rounds two-thirds empty.
   const int first = blockIdx.x;
   const int stride = gridDim.x;
+  const int units = 2 * batch;
 
   if (warp == 0) {
     // ---- producer: one 16 KiB bulk copy per image ------------------------------------------------
     if (elect_one()) {
       int it = 0;
-      for (int img = first; img < batch; img += stride, ++it) {
+      for (int u = first; u < units; u += stride, ++it) {
         const int b = it % C2_BUFS;
         mbar_wait(&img_empty[b], ((it / C2_BUFS) & 1) ^ 1, 10);
         mbar_arrive_expect_tx(&img_full[b], C2_IMG_BYTES);
-        bulk_load_1d(s_img + b * C2_IMG_BYTES, p1_planes + static_cast<size_t>(img) * C2_IMG_BYTES, C2_IMG_BYTES, &img_full[b]);
+        bulk_load_1d(s_img + b * C2_IMG_BYTES, p1_planes + static_cast<size_t>(u >> 1) * C2_IMG_BYTES, C2_IMG_BYTES, &img_full[b]);
       }
     }
   } else if (warp == 1) {
@@ -116,16 +121,16 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
       const UmmaDescBase w_desc = umma_desc_base(smem_u32(s_w), C2_OUT * 16, 128, UMMA_SWIZZLE_NONE);
       if (w_packed != nullptr) mbar_wait(&w_full, 0, 14);
       int it = 0;
-      for (int img = first; img < batch; img += stride, ++it) {
+      for (int u = first; u < units; u += stride, ++it) {
         const int b = it % C2_BUFS;
-        const int a = it & 1;
-        mbar_wait(&acc_empty[a], ((it >> 1) & 1) ^ 1, 11);
+        const int a = it % C2_ACC;
+        mbar_wait(&acc_empty[a], ((it / C2_ACC) & 1) ^ 1, 11);
         mbar_wait(&img_full[b], (it / C2_BUFS) & 1, 12);
         tc_fence_after();
         const UmmaDescBase a_base = umma_desc_base(smem_u32(s_img + b * C2_IMG_BYTES), PL_PLANE_BYTES, 128, UMMA_SWIZZLE_NONE);
-#pragma unroll 1
-        for (int t = 0; t < 2; ++t) {
-          const uint32_t d_tmem = tmem_base + a * 128 + t * 64;
+        {
+          const int t = u & 1;
+          const uint32_t d_tmem = tmem_base + a * 64;
           const int tile_off = t * 128 * 16;
 #pragma unroll
           for (int tap = 0; tap < 25; ++tap) {
@@ -151,12 +156,13 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
     const int w_px = lane & 15;            // column inside the 16-wide grid
     const int h_sub = lane >> 4;           // 0/1: row inside the warp's row pair
     int it = 0;
-    for (int img = first; img < batch; img += stride, ++it) {
-      const int a = it & 1;
-      mbar_wait(&acc_full[a], (it >> 1) & 1, 13);
+    for (int u = first; u < units; u += stride, ++it) {
+      const int a = it % C2_ACC;
+      const int img = u >> 1;
+      mbar_wait(&acc_full[a], (it / C2_ACC) & 1, 13);
       tc_fence_after();
-#pragma unroll 1
-      for (int t = 0; t < 2; ++t) {
+      {
+        const int t = u & 1;
         const int h = t * 8 + q * 2 + h_sub;         // image row of this thread's pixel
         const int ph = t * 4 + q, pw = w_px >> 1;    // pooled coordinates of its window
         const bool writer = (lane < 16) && ((lane & 1) == 0) && pw < 7 && ph < 7;
@@ -165,7 +171,7 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
 #pragma unroll
         for (int cb = 0; cb < CH; cb += 32) {
           uint32_t r[32];
-          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 128 + t * 64 + c0 + cb, r);
+          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + a * 64 + c0 + cb, r);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[cb + j] = fmaxf(__uint_as_float(r[j]) + s_bias[c0 + cb + j], 0.0f);
@@ -250,7 +256,7 @@ extern "C" int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const v
     DTM_CUDA_OK(cudaFuncSetAttribute(conv2_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C2_SMEM));
     configured = true;
   }
-  const int grid = min(batch, device_sm_count());
+  const int grid = min(2 * batch, device_sm_count());
   auto args = [&](auto kern) -> int {
     DTM_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(lrn ? 256 : 384), C2_SMEM, s, static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
                                     static_cast<const uint8_t*>(packed), bias, batch, static_cast<__nv_bfloat16*>(p2), static_cast<uint8_t*>(argmax),

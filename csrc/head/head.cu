@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(256)
 head_forward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, const float* __restrict__ w,
                     const float* __restrict__ bias, const int* __restrict__ labels, float grad_scale, float loss_scale,
                     float* __restrict__ logits_out, float* __restrict__ probs_out, float* __restrict__ dlogits,
-                    dtm_train_state* __restrict__ state, int early_weights) {
+                    __nv_bfloat16* __restrict__ dh, float inv_keep, dtm_train_state* __restrict__ state, int early_weights) {
   __shared__ float s_w[HF_CHUNK * HF_PITCH];   // 44 KiB: the weight rows of the current chunk, shared by the CTA's 8 rows
   __shared__ float s_loss[8], s_corr[8];
   __shared__ unsigned int s_nan;
@@ -37,25 +37,27 @@ head_forward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, 
 #pragma unroll
   for (int c = 0; c < NCLS; ++c) acc[c] = 0.0f;
   const __nv_bfloat16* hr = h + static_cast<size_t>(row_ok ? row : 0) * hidden;
+  // stage one chunk of weight rows with 16-byte loads, several in flight per thread (a serial 4-byte loop cost 20 us)
+  auto stage_chunk = [&](int k0, int kc) {
+    const float4* w4 = reinterpret_cast<const float4*>(w + static_cast<size_t>(k0) * NCLS);
+    const int n4 = (kc * NCLS) >> 2;
+#pragma unroll 5
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+      const float4 v = w4[i];
+      const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const int idx = 4 * i + t;
+        s_w[(idx / NCLS) * HF_PITCH + idx % NCLS] = e[t];
+      }
+    }
+    for (int idx = (n4 << 2) + threadIdx.x; idx < kc * NCLS; idx += blockDim.x)
+      s_w[(idx / NCLS) * HF_PITCH + idx % NCLS] = w[static_cast<size_t>(k0) * NCLS + idx];
+  };
   for (int k0 = 0; k0 < hidden; k0 += HF_CHUNK) {
     const int kc = min(HF_CHUNK, hidden - k0);
     __syncthreads();
-    {  // stage the chunk with 16-byte loads, several in flight per thread (a serial 4-byte loop here cost 20 us)
-      const float4* w4 = reinterpret_cast<const float4*>(w + static_cast<size_t>(k0) * NCLS);
-      const int n4 = (kc * NCLS) >> 2;
-#pragma unroll 5
-      for (int i = threadIdx.x; i < n4; i += blockDim.x) {
-        const float4 v = w4[i];
-        const float e[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          const int idx = 4 * i + t;
-          s_w[(idx / NCLS) * HF_PITCH + idx % NCLS] = e[t];
-        }
-      }
-      for (int idx = (n4 << 2) + threadIdx.x; idx < kc * NCLS; idx += blockDim.x)
-        s_w[(idx / NCLS) * HF_PITCH + idx % NCLS] = w[static_cast<size_t>(k0) * NCLS + idx];
-    }
+    stage_chunk(k0, kc);
     __syncthreads();
     if (k0 == 0) { pdl_wait(); pdl_launch_dependents(); }   // the weights above are older than the preceding kernel; h is not
     if (row_ok) {
@@ -72,6 +74,9 @@ head_forward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, 
   for (int c = 0; c < NCLS; ++c) acc[c] = warp_sum(acc[c]) + bias[c];
 
   float my_loss = 0.0f, my_corr = 0.0f;
+  float d[NCLS];   // dlogits of this warp's row (lane 0 computes, everyone gets a copy below)
+#pragma unroll
+  for (int c = 0; c < NCLS; ++c) d[c] = 0.0f;
   if (row_ok && lane == 0) {
     float mx = acc[0];
 #pragma unroll
@@ -99,12 +104,40 @@ head_forward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, 
       const float loss = (mx - target) + __logf(sum);
       if (dlogits) {
 #pragma unroll
-        for (int c = 0; c < NCLS; ++c)
-          dlogits[static_cast<size_t>(row) * NCLS + c] = (e[c] * inv - (c == y ? 1.0f : 0.0f)) * grad_scale;
+        for (int c = 0; c < NCLS; ++c) {
+          d[c] = (e[c] * inv - (c == y ? 1.0f : 0.0f)) * grad_scale;
+          dlogits[static_cast<size_t>(row) * NCLS + c] = d[c];
+        }
       }
       my_loss = loss * loss_scale;
       my_corr = greater == 0 ? loss_scale : 0.0f;
       if (!(fabsf(loss) <= 3.0e38f)) atomicOr(&s_nan, 1u);  // catches NaN and Inf
+    }
+  }
+  // gradient w.r.t. the hidden activation, dH = (dlogits . W^T) * inv_keep * [h > 0], while the weight rows are still in
+  // shared memory: the fc gradient GEMMs that follow need nothing else from the head, so its weight/bias gradients
+  // (head_backward) leave the critical path
+  if (dh != nullptr && dlogits != nullptr && labels != nullptr) {
+#pragma unroll
+    for (int c = 0; c < NCLS; ++c) d[c] = __shfl_sync(0xffffffffu, d[c], 0);
+    for (int k0 = 0; k0 < hidden; k0 += HF_CHUNK) {
+      const int kc = min(HF_CHUNK, hidden - k0);
+      if (hidden > HF_CHUNK) {   // more than one chunk: the buffer holds the last one, stage again
+        __syncthreads();
+        stage_chunk(k0, kc);
+        __syncthreads();
+      }
+      if (row_ok) {
+#pragma unroll 4
+        for (int k = lane; k < kc; k += 32) {
+          const float hv = __bfloat162float(hr[k0 + k]);
+          const float* wk = s_w + k * HF_PITCH;
+          float g = 0.0f;
+#pragma unroll
+          for (int c = 0; c < NCLS; ++c) g = fmaf(d[c], wk[c], g);
+          dh[static_cast<size_t>(row) * hidden + k0 + k] = __float2bfloat16(hv > 0.0f ? g * inv_keep : 0.0f);
+        }
+      }
     }
   }
   if (lane == 0) { s_loss[wid] = my_loss; s_corr[wid] = my_corr; }
@@ -124,7 +157,7 @@ constexpr int HB_COLS = 32;
 __global__ void __launch_bounds__(256)
 head_backward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden, const float* __restrict__ w,
                      const float* __restrict__ dlogits, float inv_keep, __nv_bfloat16* __restrict__ dh,
-                     float* __restrict__ dw, float* __restrict__ db_out, float* __restrict__ db_hidden) {
+                     float* __restrict__ dw, float* __restrict__ db_out, float* __restrict__ db_hidden, int dh_ready) {
   __shared__ float s_red[8][NCLS + 1][HB_COLS + 1];
   const int kk = threadIdx.x & 31;
   const int r = threadIdx.x >> 5;
@@ -149,8 +182,13 @@ head_backward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden,
       float g = 0.0f;
 #pragma unroll
       for (int c = 0; c < NCLS; ++c) { g = fmaf(d[c], wk[c], g); adw[c] = fmaf(hv, d[c], adw[c]); }
-      const __nv_bfloat16 gb = __float2bfloat16(hv > 0.0f ? g * inv_keep : 0.0f);
-      dh[static_cast<size_t>(b) * hidden + k] = gb;
+      __nv_bfloat16 gb;
+      if (dh_ready) {   // head_forward already produced dH: only its column sums (hidden-bias gradient) are needed
+        gb = dh[static_cast<size_t>(b) * hidden + k];
+      } else {
+        gb = __float2bfloat16(hv > 0.0f ? g * inv_keep : 0.0f);
+        dh[static_cast<size_t>(b) * hidden + k] = gb;
+      }
       adb += __bfloat162float(gb);
     }
   }
@@ -179,19 +217,20 @@ head_backward_kernel(const __nv_bfloat16* __restrict__ h, int batch, int hidden,
 }  // namespace dtm
 
 extern "C" int dtm_head_forward(const void* h, int batch, int hidden, const float* w, const float* bias, const int* labels,
-                                float grad_scale, float loss_scale, float* logits, float* probs, float* dlogits,
-                                dtm_train_state* state, void* stream) {
+                                float grad_scale, float loss_scale, float* logits, float* probs, float* dlogits, void* dh,
+                                float inv_keep, dtm_train_state* state, void* stream) {
   using namespace dtm;
   if (batch <= 0 || hidden <= 0) return dtm_fail("head_forward: batch and hidden must be positive");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   DTM_CUDA_OK(launch_pdl(head_forward_kernel, dim3((batch + 7) / 8), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(h), batch, hidden,
-                         w, bias, labels, grad_scale, loss_scale, logits, probs, dlogits, state, pdl_mode() == 2 ? 1 : 0));
+                         w, bias, labels, grad_scale, loss_scale, logits, probs, dlogits, static_cast<__nv_bfloat16*>(dh), inv_keep, state,
+                         pdl_mode() == 2 ? 1 : 0));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
 extern "C" int dtm_head_backward(const void* h, int batch, int hidden, const float* w, const float* dlogits, float inv_keep,
-                                 void* dh, float* dw, float* db_out, float* db_hidden, void* stream) {
+                                 void* dh, float* dw, float* db_out, float* db_hidden, int dh_ready, void* stream) {
   using namespace dtm;
   if (batch <= 0 || hidden <= 0) return dtm_fail("head_backward: batch and hidden must be positive");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -199,7 +238,7 @@ extern "C" int dtm_head_backward(const void* h, int batch, int hidden, const flo
   int split = 1;
   while (col_blocks * split < 2 * device_sm_count() && split * 16 <= batch && split < 16) split *= 2;
   DTM_CUDA_OK(launch_pdl(head_backward_kernel, dim3(col_blocks, split), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(h), batch,
-                         hidden, w, dlogits, inv_keep, static_cast<__nv_bfloat16*>(dh), dw, db_out, db_hidden));
+                         hidden, w, dlogits, inv_keep, static_cast<__nv_bfloat16*>(dh), dw, db_out, db_hidden, dh_ready));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -17,6 +17,7 @@ struct UpdateScalars {
   float lr;          // decayed learning rate (Adam: already multiplied by the bias-correction factor)
   float ema_keep;    // d
   float grad_scale;  // 1 / world_size
+  float lr_plain;    // decayed learning rate without the Adam factor (what the summaries report)
 };
 
 __device__ __forceinline__ UpdateScalars make_update_scalars(const dtm_update_config& cfg, const dtm_train_state* st,
@@ -25,6 +26,7 @@ __device__ __forceinline__ UpdateScalars make_update_scalars(const dtm_update_co
   const long long step = st->global_step;
   const float exponent = cfg.decay_steps > 0 ? floorf(static_cast<float>(step / cfg.decay_steps)) : 0.0f;
   float lr = cfg.base_lr * powf(cfg.decay_rate, exponent);
+  u.lr_plain = lr;
   if (cfg.optimizer == DTM_OPT_ADAM) lr *= sqrtf(1.0f - st->beta2_power) / (1.0f - st->beta1_power);
   u.lr = lr;
   const float t = static_cast<float>(step);
@@ -139,29 +141,49 @@ __device__ __forceinline__ void pack_conv2_vec4(const dtm_update_config& cfg, in
 // End-of-step bookkeeping, executed by exactly one thread after every element has been updated:
 // publishes the step's metrics, advances the loss moving averages (mnist_input.py:288-290, decay 0.9),
 // the Adam beta powers and global_step, and clears the per-step accumulators.
+// Closes the step: loss bookkeeping, beta powers, global_step.  Called by EVERY thread of the (single) CTA that finishes
+// last; blockDim.x >= DTM_MAX_SEGMENTS.  The per-variable work runs one thread per variable and thread 0 loads all of its
+// scalars before its first store, so the step ends after ~2 dependent memory round trips instead of ~25 (this tail is
+// on the critical path of every training step).
 __device__ __forceinline__ void finish_step(const dtm_update_config& cfg, dtm_train_state* st, float lr_plain) {
-  const float xent = st->loss_sum;
-  float total = xent;
-  for (int s = 0; s < cfg.n_segments; ++s) {
-    const float wl = 0.5f * cfg.seg_wd[s] * st->wl_sum[s];
-    st->last_wl[s] = wl;
-    total += wl;
-    st->loss_avg[s] -= 0.1f * (st->loss_avg[s] - wl);
-    st->wl_sum[s] = 0.0f;
+  __shared__ float s_fin_wl[DTM_MAX_SEGMENTS];
+  const int t = threadIdx.x;
+  if (t < DTM_MAX_SEGMENTS) {
+    float wl = 0.0f;
+    if (t < cfg.n_segments) {
+      const float sum = st->wl_sum[t];
+      const float avg = st->loss_avg[t];
+      wl = 0.5f * cfg.seg_wd[t] * sum;
+      st->last_wl[t] = wl;
+      st->loss_avg[t] = avg - 0.1f * (avg - wl);
+      st->wl_sum[t] = 0.0f;
+    }
+    s_fin_wl[t] = wl;
   }
-  st->loss_avg[DTM_MAX_SEGMENTS] -= 0.1f * (st->loss_avg[DTM_MAX_SEGMENTS] - xent);
-  st->loss_avg[DTM_MAX_SEGMENTS + 1] -= 0.1f * (st->loss_avg[DTM_MAX_SEGMENTS + 1] - total);
-  st->last_xent = xent;
-  st->last_total = total;
-  st->last_acc = st->correct;
-  st->last_lr = lr_plain;
-  st->loss_sum = 0.0f;
-  st->correct = 0.0f;
-  if (cfg.optimizer == DTM_OPT_ADAM) {
-    st->beta1_power *= cfg.beta1;
-    st->beta2_power *= cfg.beta2;
+  __syncthreads();
+  if (t == 0) {
+    const float xent = st->loss_sum;
+    const float acc = st->correct;
+    const float avg_x = st->loss_avg[DTM_MAX_SEGMENTS];
+    const float avg_t = st->loss_avg[DTM_MAX_SEGMENTS + 1];
+    const float b1 = st->beta1_power, b2 = st->beta2_power;
+    const long long step = st->global_step;
+    float total = xent;
+    for (int s = 0; s < cfg.n_segments; ++s) total += s_fin_wl[s];   // same summation order as ever
+    st->loss_avg[DTM_MAX_SEGMENTS] = avg_x - 0.1f * (avg_x - xent);
+    st->loss_avg[DTM_MAX_SEGMENTS + 1] = avg_t - 0.1f * (avg_t - total);
+    st->last_xent = xent;
+    st->last_total = total;
+    st->last_acc = acc;
+    st->last_lr = lr_plain;
+    st->loss_sum = 0.0f;
+    st->correct = 0.0f;
+    if (cfg.optimizer == DTM_OPT_ADAM) {
+      st->beta1_power = b1 * cfg.beta1;
+      st->beta2_power = b2 * cfg.beta2;
+    }
+    st->global_step = step + 1;
   }
-  st->global_step += 1;
 }
 
 }  // namespace dtm

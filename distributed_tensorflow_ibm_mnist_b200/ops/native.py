@@ -27,8 +27,8 @@ _lib.register("dtm_conv2_wgrad", [P, P, I, P, P])
 _lib.register("dtm_unpool2", [P, P, P, I, I, P, P, P])
 _lib.register("dtm_colsum_bf16", [P, I, I, P, P])
 _lib.register("dtm_set_pdl_mode", [I])
-_lib.register("dtm_head_forward", [P, I, I, P, P, P, F, F, P, P, P, P, P])
-_lib.register("dtm_head_backward", [P, I, I, P, P, F, P, P, P, P, P])
+_lib.register("dtm_head_forward", [P, I, I, P, P, P, F, F, P, P, P, P, F, P, P])
+_lib.register("dtm_head_backward", [P, I, I, P, P, F, P, P, P, P, I, P])
 _lib.register("dtm_fused_update", [P, P, P, P, P, P, P, P, F, P])
 _lib.register("dtm_fused_update_range", [P, P, P, P, P, P, P, P, F, I, I, I, I, P])
 _lib.register("dtm_state_init", [P, c_longlong, F, F, P])
@@ -145,16 +145,19 @@ class pdl_mode:
         return False
 
 
-def head_forward(h, w, bias, labels, *, grad_scale, loss_scale, logits=None, probs=None, dlogits=None, state=None):
+def head_forward(h, w, bias, labels, *, grad_scale, loss_scale, logits=None, probs=None, dlogits=None, state=None, dh=None,
+                 inv_keep=1.0):
+    """fc10 + softmax cross-entropy (+ dlogits, + dH when ``dh`` is given: see ``dtm_head_forward``)."""
     batch, hidden = h.shape
     check(_L().dtm_head_forward(ptr(h), batch, hidden, ptr(w), ptr(bias), ptr(labels), float(grad_scale), float(loss_scale),
-                                ptr(logits), ptr(probs), ptr(dlogits), ptr(state), current_stream()), "head_forward")
+                                ptr(logits), ptr(probs), ptr(dlogits), ptr(dh), float(inv_keep), ptr(state), current_stream()),
+          "head_forward")
 
 
-def head_backward(h, w, dlogits, dh, dw, db_out, db_hidden, *, inv_keep=1.0):
+def head_backward(h, w, dlogits, dh, dw, db_out, db_hidden, *, inv_keep=1.0, dh_ready=False):
     batch, hidden = h.shape
     check(_L().dtm_head_backward(ptr(h), batch, hidden, ptr(w), ptr(dlogits), float(inv_keep), ptr(dh), ptr(dw), ptr(db_out),
-                                 ptr(db_hidden), current_stream()), "head_backward")
+                                 ptr(db_hidden), int(dh_ready), current_stream()), "head_backward")
 
 
 def fused_update(cfg: UpdateConfig, state, w, grad, slot0, slot1, ema, w_bf16, *, grad_scale=1.0):

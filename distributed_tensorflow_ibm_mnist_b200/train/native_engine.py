@@ -52,6 +52,10 @@ class NativeEngine:
         self._graphs: dict[int, torch.cuda.CUDAGraph] = {}
         self._side = torch.cuda.Stream(device=self.device)
         self._comm_stream = torch.cuda.Stream(device=self.device)
+        self._head_stream = torch.cuda.Stream(device=self.device)
+        # dH inside head_forward pays off while the head's weight rows fit one shared-memory staging chunk (1024 hidden units);
+        # beyond that (the wide preset) the forward kernel would stage every chunk twice
+        self._fuse_dh = (spec.fc2 or spec.fc1) <= 1024
         self._fork_ev = [torch.cuda.Event() for _ in range(10)]
         # gradient buckets in flat-buffer order: the fc/head variables (93 % of the bytes, ready right after the first
         # backward GEMMs) and the conv variables (ready last).  With >1 rank bucket 0 is reduced + updated on its own
@@ -197,9 +201,13 @@ class NativeEngine:
                              epilogue=native.EPI_BIAS_RELU_BF16, bias=f.weight("local4/biases")); n += 1
             h = self.h2
         if self._on("head_fwd"):
+            # training: the head also emits dH, so the fc gradient GEMMs can follow it directly (head_backward then only
+            # produces weight / bias gradients, beside those GEMMs)
             native.head_forward(h, f.weight("softmax_linear/weights"), f.weight("softmax_linear/biases"), labels,
                                 grad_scale=1.0 / B, loss_scale=1.0 / B, logits=self.logits, probs=self.probs,
-                                dlogits=self.dlogits if training else None, state=state); n += 1
+                                dlogits=self.dlogits if training else None, state=state,
+                                dh=self.dh_last if (training and labels is not None and self._fuse_dh) else None,
+                                inv_keep=1.0 / s.keep_prob if drop_here else 1.0); n += 1
         self._mark("head_fwd")
         if count is not None:
             count[0] += n
@@ -213,10 +221,21 @@ class NativeEngine:
         n = 0
         h = self.h2 if s.fc2 else self.h1
         inv_keep = 1.0 / s.keep_prob if (s.keep_prob < 1.0 and not s.fc2) else 1.0
-        if self._on("head_bwd"):
+        main = torch.cuda.current_stream()
+        if self._on("head_bwd") and not self._fuse_dh:
             native.head_backward(h, f.weight("softmax_linear/weights"), self.dlogits, self.dh_last,
                                  f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
                                  f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep); n += 1
+        elif self._on("head_bwd"):
+            # third branch: dH already exists (head_forward), the head's own gradients run beside the fc GEMMs
+            self._fork_ev[6].record(main)
+            self._head_stream.wait_event(self._fork_ev[6])
+            with torch.cuda.stream(self._stream(self._head_stream)):
+                native.head_backward(h, f.weight("softmax_linear/weights"), self.dlogits, self.dh_last,
+                                     f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
+                                     f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep,
+                                     dh_ready=True); n += 1
+                self._fork_ev[7].record(self._head_stream)
         self._mark("head_bwd")
         if s.fc2:
             # dW4 = h1^T . dY2 ; dY1 = (dY2 . W4^T) * [h1 > 0] ; db3 = colsum(dY1)
@@ -227,7 +246,6 @@ class NativeEngine:
             dy1 = self.dh1
         else:
             dy1 = self.dh_last
-        main = torch.cuda.current_stream()
         lo0, hi0 = self.buckets[0]
         # fork: the two big fc GEMMs are independent
         self._fork_ev[0].record(main)
@@ -248,6 +266,8 @@ class NativeEngine:
             self._fork_ev[4].record(main)
             self._comm_stream.wait_event(self._fork_ev[4])
             self._comm_stream.wait_event(self._fork_ev[1])
+            if self._on("head_bwd") and self._fuse_dh:
+                self._comm_stream.wait_event(self._fork_ev[7])
             with torch.cuda.stream(self._stream(self._comm_stream)):
                 if self.sharded:
                     self.comm.fused_allreduce_update(self.cfg, self.state, f, lo0, hi0, finish=False, overlapped=True)
@@ -279,6 +299,8 @@ class NativeEngine:
         self._mark("conv1_wgrad")
         main.wait_event(self._fork_ev[1])
         main.wait_event(self._fork_ev[3])
+        if self._on("head_bwd") and self._fuse_dh:
+            main.wait_event(self._fork_ev[7])
         self._mark("join_wgrad")
         if early_update:
             main.wait_event(self._fork_ev[5])

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define DTM_ABI_VERSION 5
+#define DTM_ABI_VERSION 6
 
 /* GEMM epilogues */
 #define DTM_EPI_STORE_F32 0      /* D(fp32)  = alpha * acc          (split-K: red.add into pre-zeroed D) */
@@ -154,14 +154,16 @@ int dtm_colsum_bf16(const void* x, int M, int N, float* out, void* stream);
 
 /* ---- classifier head + loss (reference: mnist_input.py:200-205, :224-226, :238-240; main.py:138) ---------------- */
 /* h bf16 [B][hidden]; w fp32 [hidden][10]; labels int32 (may be NULL for inference).  Any of logits / probs /
- * dlogits ([B][10] fp32) / state may be NULL.  loss_scale is 1/B so that state->loss_sum is the batch mean. */
+ * dlogits ([B][10] fp32) / dh / state may be NULL.  loss_scale is 1/B so that state->loss_sum is the batch mean.
+ * dh (needs labels and dlogits): bf16 [B][hidden] = (dlogits . w^T) * inv_keep * [h > 0], computed while the weight rows are
+ * still in shared memory, so that the gradient GEMMs of the layer below can start without waiting for dtm_head_backward. */
 int dtm_head_forward(const void* h, int batch, int hidden, const float* w, const float* bias, const int* labels,
-                     float grad_scale, float loss_scale, float* logits, float* probs, float* dlogits,
+                     float grad_scale, float loss_scale, float* logits, float* probs, float* dlogits, void* dh, float inv_keep,
                      dtm_train_state* state, void* stream);
-/* dh bf16 [B][hidden] = (dlogits . w^T) * [h > 0] * inv_keep ; dw [hidden][10], db_out [10], db_hidden [hidden]
- * (may be NULL) are accumulated (red.add). */
+/* dw [hidden][10], db_out [10], db_hidden [hidden] (may be NULL) are accumulated (red.add).  dh_ready = 0: also computes and
+ * stores dh as above; dh_ready = 1: dh was produced by dtm_head_forward and is only read (for db_hidden). */
 int dtm_head_backward(const void* h, int batch, int hidden, const float* w, const float* dlogits, float inv_keep, void* dh,
-                      float* dw, float* db_out, float* db_hidden, void* stream);
+                      float* dw, float* db_out, float* db_hidden, int dh_ready, void* stream);
 
 /* ---- optimizer (reference: mnist_input.py:246-270) ------------------------------------------------------------ */
 /* One kernel: lr schedule, weight decay, SGD/Momentum/Adam, EMA(0.9999), bf16 shadow weights, loss averages,

@@ -113,13 +113,14 @@ def test_conv1_forward(channels, lrn):
     assert (picked - p1.permute(0, 2, 3, 1).reshape(B, 196, 32)).abs().max().item() <= 1e-3 * p1.abs().max().item()
 
 
-@pytest.mark.parametrize("lrn", [False, True])
-def test_conv2_forward(lrn):
+@pytest.mark.parametrize("lrn,B", [(False, 150), (True, 150), (False, 777)])
+def test_conv2_forward(lrn, B):
     native, layouts = _native()
     from distributed_tensorflow_ibm_mnist_b200.models.oracle import tf_lrn
 
     g = torch.Generator().manual_seed(12)
-    B = 150  # > #SMs would be 148: exercises the persistent loop with uneven work
+    # 150: uneven work over the persistent CTAs; 777: > 10 work units per CTA, so the image-buffer ring (3) and the TMEM
+    # accumulator ring (4) wrap several times
     p1 = _bf(torch.relu(torch.randn(B, 14, 14, 32, generator=g)))
     w2 = _bf(torch.randn(5, 5, 32, 64, generator=g) * 0.05)
     b2 = torch.randn(64, generator=g) * 0.1
@@ -139,10 +140,11 @@ def test_conv2_forward(lrn):
     assert (picked - want).abs().max().item() <= 2e-2 * want.abs().max().item()
 
 
-def test_unpool2_and_conv2_backward():
+@pytest.mark.parametrize("B", [75, 640])
+def test_unpool2_and_conv2_backward(B):
     native, layouts = _native()
     g = torch.Generator().manual_seed(13)
-    B = 75
+    # 640 images = 1280 work units over <= 148 CTAs: every pipeline ring of dgrad / wgrad wraps several times
     p1 = _bf(torch.relu(torch.randn(B, 14, 14, 32, generator=g)))
     w2 = _bf(torch.randn(5, 5, 32, 64, generator=g) * 0.05)
     dp2 = _bf(torch.randn(B, 49, 64, generator=g))
@@ -201,7 +203,7 @@ def test_conv1_wgrad():
 
 
 # ----------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("hidden", [1024, 192])
+@pytest.mark.parametrize("hidden", [1024, 192, 2560])
 def test_head_forward_backward(hidden):
     native, _ = _native()
     g = torch.Generator().manual_seed(15)
@@ -215,8 +217,9 @@ def test_head_forward_backward(hidden):
     logits = torch.empty(B, 10, device=DEV)
     probs = torch.empty(B, 10, device=DEV)
     dlog = torch.empty(B, 10, device=DEV)
+    dh_fused = torch.empty(B, hidden, dtype=torch.bfloat16, device=DEV)
     native.head_forward(h.to(torch.bfloat16).to(DEV), w.to(DEV), b.to(DEV), y.to(DEV), grad_scale=1.0 / B, loss_scale=1.0 / B,
-                        logits=logits, probs=probs, dlogits=dlog, state=state)
+                        logits=logits, probs=probs, dlogits=dlog, state=state, dh=dh_fused, inv_keep=2.0)
     hv = h.clone().requires_grad_(True)
     wv = w.clone().requires_grad_(True)
     bv = b.clone().requires_grad_(True)
@@ -241,6 +244,17 @@ def test_head_forward_backward(hidden):
     assert _rel_err(dw.cpu(), wv.grad) < 1e-4
     assert _rel_err(dbo.cpu(), bv.grad) < 1e-4
     assert _rel_err(dbh.cpu(), _bf(want_dh).sum(0)) < 1e-2
+    # dH fused into the forward kernel (2560 > one staging chunk: exercises the re-staging path), and the backward kernel
+    # in "dh ready" mode: same weight / bias gradients, hidden-bias gradient from the stored dH
+    assert _rel_err(dh_fused.cpu(), want_dh) < 1e-2
+    assert _rel_err(dh_fused.float().cpu(), dh.float().cpu()) < 1e-2
+    dw2 = torch.zeros(hidden, 10, device=DEV)
+    dbo2 = torch.zeros(10, device=DEV)
+    dbh2 = torch.zeros(hidden, device=DEV)
+    native.head_backward(h.to(torch.bfloat16).to(DEV), w.to(DEV), dlog, dh_fused, dw2, dbo2, dbh2, inv_keep=2.0, dh_ready=True)
+    assert _rel_err(dw2.cpu(), wv.grad) < 1e-4
+    assert _rel_err(dbo2.cpu(), bv.grad) < 1e-4
+    assert _rel_err(dbh2.cpu(), _bf(want_dh).sum(0)) < 1e-2
 
 
 def test_head_flags_nan():
