@@ -113,8 +113,10 @@ extern "C" int dtm_conv1_wgrad(const void* x, int in_is_float, int channels, con
   const int grid = min(batch, 4 * device_sm_count());   // 3-4 CTAs per SM: the loop is LDS/FMA latency bound
   const __nv_bfloat16* g = static_cast<const __nv_bfloat16*>(grad_pooled);
   const uint8_t* a = static_cast<const uint8_t*>(argmax);
-  if (channels == 1) DTM_CUDA_OK(launch_pdl(conv1_wgrad_kernel<1>, dim3(grid), dim3(256), 0, s, x, in_is_float, g, a, batch, dw, db));
-  else               DTM_CUDA_OK(launch_pdl(conv1_wgrad_kernel<3>, dim3(grid), dim3(256), 0, s, x, in_is_float, g, a, batch, dw, db));
+  // plain launches: in the training schedule this kernel sits on a side stream behind an event (it joins that stream's
+  // own history with dgrad's), and a programmatic edge is only defined towards a single predecessor
+  if (channels == 1) conv1_wgrad_kernel<1><<<grid, 256, 0, s>>>(x, in_is_float, g, a, batch, dw, db);
+  else               conv1_wgrad_kernel<3><<<grid, 256, 0, s>>>(x, in_is_float, g, a, batch, dw, db);
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -151,10 +151,8 @@ extern "C" int dtm_conv2_wgrad(const void* p1_planes, const void* dz2_planes, in
     configured = true;
   }
   const int gx = min(batch, max(1, device_sm_count() / 2));
-  // plain launch: in the training schedule this kernel joins two streams (dgrad's and the side stream's own history); a
-  // programmatic edge is only defined towards a single predecessor
-  conv2_wgrad_kernel<<<dim3(gx, 2), 256, WG_SMEM, s>>>(static_cast<const uint8_t*>(p1_planes),
-                                                      static_cast<const uint8_t*>(dz2_planes), batch, dw2);
+  DTM_CUDA_OK(launch_pdl(conv2_wgrad_kernel, dim3(gx, 2), dim3(256), WG_SMEM, s, static_cast<const uint8_t*>(p1_planes),
+                         static_cast<const uint8_t*>(dz2_planes), batch, dw2));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

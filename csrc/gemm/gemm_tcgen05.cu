@@ -14,6 +14,7 @@
 #include "../common/philox.cuh"
 #include "../common/host_util.h"
 #include "../../include/dtm_b200.h"
+#include "../conv/plane_layout.cuh"
 
 namespace dtm {
 
@@ -37,6 +38,11 @@ struct GemmArgs {
   float keep_prob;              // dropout keep probability; >= 1 disables
   uint64_t seed;
   const long long* step_ptr;    // device global_step, makes the dropout mask step dependent
+  // DTM_EPI_MASK_UNPOOL_BF16: D is the gradient of the 7x7x64 pooled conv2 activation ([M][49*64], one N tile = one pooled
+  // pixel); besides D the epilogue routes it through the pooling arg-max into the 14x14 plane-layout tensor conv2's backward
+  // kernels consume - the separate un-pooling kernel and its launch gap disappear from the step's critical path
+  const uint8_t* argmax;        // [M][49][64]
+  uint8_t* planes;              // [M] plane-layout images, 64 channels
 };
 
 // STAGES = 4: two CTAs per SM (grids larger than the machine, short K).  STAGES = 8: one CTA per SM with twice the
@@ -206,7 +212,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 }
               }
             }
-          } else if (g.epilogue == DTM_EPI_MASK_BF16) {
+          } else if (g.epilogue == DTM_EPI_MASK_BF16 || g.epilogue == DTM_EPI_MASK_UNPOOL_BF16) {
             const uint4 rv = *reinterpret_cast<const uint4*>(ref + j);
             const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
@@ -221,6 +227,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           o.z = pack_bf16x2(v[4], v[5]);
           o.w = pack_bf16x2(v[6], v[7]);
           *reinterpret_cast<uint4*>(out + j) = o;
+          if (g.epilogue == DTM_EPI_MASK_UNPOOL_BF16) {
+            // this thread holds 8 channels of pooled pixel pp = n / 64 of image m: write the four positions of its 2x2
+            // window (the arg-max one gets the value, the others zero) as 16-byte plane pixels
+            const int pp = n >> 6, ch = (n & 63) + j;
+            const int ph = pp / 7, pw = pp - ph * 7;
+            const uint2 av = *reinterpret_cast<const uint2*>(g.argmax + (static_cast<size_t>(m) * 49 + pp) * 64 + ch);
+            const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
+            uint8_t* img = g.planes + static_cast<size_t>(m) * plane_image_bytes(64);
+#pragma unroll
+            for (int d = 0; d < 4; ++d) {
+              uint32_t z[4];
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                const uint32_t a0 = ((t < 2 ? av.x : av.y) >> (16 * (t & 1))) & 0xFF;
+                const uint32_t a1 = ((t < 2 ? av.x : av.y) >> (16 * (t & 1) + 8)) & 0xFF;
+                z[t] = (a0 == static_cast<uint32_t>(d) ? (ow[t] & 0x0000FFFFu) : 0u) | (a1 == static_cast<uint32_t>(d) ? (ow[t] & 0xFFFF0000u) : 0u);
+              }
+              *reinterpret_cast<uint4*>(img + plane_offset(2 * ph + (d >> 1), 2 * pw + (d & 1), ch)) = make_uint4(z[0], z[1], z[2], z[3]);
+            }
+          }
         }
       }
     }
@@ -254,16 +280,19 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmA
 
 }  // namespace dtm
 
-extern "C" int dtm_gemm_bf16(const void* a, int a_mn_major, const void* b, int b_mn_major, void* d, int M, int N,
-                             int K, int ldd, int epilogue, const float* bias, const void* ref, float alpha,
-                             float keep_prob, uint64_t seed, const long long* step_ptr, int split_k, void* stream) {
-  using namespace dtm;
+namespace dtm {
+static int gemm_run(const void* a, int a_mn_major, const void* b, int b_mn_major, void* d, int M, int N, int K, int ldd,
+                    int epilogue, const float* bias, const void* ref, float alpha, float keep_prob, uint64_t seed,
+                    const long long* step_ptr, int split_k, const void* argmax, void* planes, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0) return dtm_fail("gemm: M, N, K must be positive");
   if (N % 8 != 0 || ldd % 8 != 0) return dtm_fail("gemm: N and ldd must be multiples of 8");
   if (K % 8 != 0) return dtm_fail("gemm: K must be a multiple of 8 (16-byte TMA rows)");
   if (M % 8 != 0 && a_mn_major) return dtm_fail("gemm: MN-major A needs M % 8 == 0");
-  if (epilogue < 0 || epilogue > DTM_EPI_MASK_BF16) return dtm_fail("gemm: unknown epilogue");
-  if (epilogue == DTM_EPI_MASK_BF16 && !ref) return dtm_fail("gemm: EPI_MASK needs a reference activation");
+  if (epilogue < 0 || epilogue > DTM_EPI_MASK_UNPOOL_BF16) return dtm_fail("gemm: unknown epilogue");
+  if ((epilogue == DTM_EPI_MASK_BF16 || epilogue == DTM_EPI_MASK_UNPOOL_BF16) && !ref)
+    return dtm_fail("gemm: EPI_MASK needs a reference activation");
+  if (epilogue == DTM_EPI_MASK_UNPOOL_BF16 && (!argmax || !planes || N != 49 * 64 || ldd != N))
+    return dtm_fail("gemm: EPI_MASK_UNPOOL needs argmax, planes and N = ldd = 3136");
   const int total_kb = (K + BK - 1) / BK;
   int splits = split_k < 1 ? 1 : split_k;
   if (splits > total_kb) splits = total_kb;
@@ -292,9 +321,26 @@ extern "C" int dtm_gemm_bf16(const void* a, int a_mn_major, const void* b, int b
   g.keep_prob = keep_prob;
   g.seed = seed;
   g.step_ptr = step_ptr;
+  g.argmax = static_cast<const uint8_t*>(argmax);
+  g.planes = static_cast<uint8_t*>(planes);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (a_mn_major && b_mn_major) return launch_gemm<true, true>(ta, tb, g, splits, s);
   if (a_mn_major && !b_mn_major) return launch_gemm<true, false>(ta, tb, g, splits, s);
   if (!a_mn_major && b_mn_major) return launch_gemm<false, true>(ta, tb, g, splits, s);
   return launch_gemm<false, false>(ta, tb, g, splits, s);
+}
+}  // namespace dtm
+
+extern "C" int dtm_gemm_bf16(const void* a, int a_mn_major, const void* b, int b_mn_major, void* d, int M, int N,
+                             int K, int ldd, int epilogue, const float* bias, const void* ref, float alpha,
+                             float keep_prob, uint64_t seed, const long long* step_ptr, int split_k, void* stream) {
+  if (epilogue == DTM_EPI_MASK_UNPOOL_BF16) return dtm::dtm_fail("gemm: use dtm_gemm_mask_unpool for the un-pooling epilogue");
+  return dtm::gemm_run(a, a_mn_major, b, b_mn_major, d, M, N, K, ldd, epilogue, bias, ref, alpha, keep_prob, seed, step_ptr,
+                       split_k, nullptr, nullptr, stream);
+}
+
+extern "C" int dtm_gemm_mask_unpool(const void* dy, const void* w_bf16, const void* p2, const void* argmax, void* dp2,
+                                    void* dz2_planes, int batch, int hidden, void* stream) {
+  return dtm::gemm_run(dy, 0, w_bf16, 0, dp2, batch, 49 * 64, hidden, 49 * 64, DTM_EPI_MASK_UNPOOL_BF16, nullptr, p2, 1.0f,
+                       1.0f, 0, nullptr, 1, argmax, dz2_planes, stream);
 }

@@ -27,6 +27,7 @@ _lib.register("dtm_conv2_wgrad", [P, P, I, P, P])
 _lib.register("dtm_unpool2", [P, P, P, I, I, P, P, P])
 _lib.register("dtm_colsum_bf16", [P, I, I, P, P])
 _lib.register("dtm_set_pdl_mode", [I])
+_lib.register("dtm_gemm_mask_unpool", [P, P, P, P, P, P, I, I, P])
 _lib.register("dtm_head_forward", [P, I, I, P, P, P, F, F, P, P, P, P, F, P, P])
 _lib.register("dtm_head_backward", [P, I, I, P, P, F, P, P, P, P, I, P])
 _lib.register("dtm_fused_update", [P, P, P, P, P, P, P, P, F, P])
@@ -81,6 +82,12 @@ def gemm_bf16(a, a_mn_major, b, b_mn_major, d, M, N, K, *, epilogue=EPI_STORE_F3
                              ptr(bias), ptr(ref), float(alpha), float(keep_prob), c_uint64(seed),
                              c_void_p(step_ptr) if isinstance(step_ptr, int) else ptr(step_ptr), split_k,
                              current_stream()), "gemm_bf16")
+
+
+def gemm_mask_unpool(dy, w_bf16, p2, argmax, dp2, dz2_planes, *, batch, hidden):
+    """dP2 GEMM of the first fc layer + ReLU mask + max-pool backward into conv2's plane layout (``dtm_gemm_mask_unpool``)."""
+    check(_L().dtm_gemm_mask_unpool(ptr(dy), ptr(w_bf16), ptr(p2), ptr(argmax), ptr(dp2), ptr(dz2_planes), int(batch), int(hidden),
+                                    current_stream()), "gemm_mask_unpool")
 
 
 def conv1_fwd(x, w, bias, p1_planes, argmax, pool_raw=None, *, channels=1, lrn=False):

@@ -56,6 +56,10 @@ class NativeEngine:
         # dH inside head_forward pays off while the head's weight rows fit one shared-memory staging chunk (1024 hidden units);
         # beyond that (the wide preset) the forward kernel would stage every chunk twice
         self._fuse_dh = (spec.fc2 or spec.fc1) <= 1024
+        # programmatic dependent launch: with the small presets the step is a chain of 10-30 us kernels and hiding the launch
+        # gaps is worth 10 %.  With the wide preset the step is bound by dW3 -> optimizer update on the side streams; early-
+        # resident CTAs of the main-stream chain then take SMs away from exactly those kernels (measured: 536 -> 562 us).
+        self._pdl = 2 if self.flat.total <= (8 << 20) else 0
         self._fork_ev = [torch.cuda.Event() for _ in range(10)]
         # gradient buckets in flat-buffer order: the fc/head variables (93 % of the bytes, ready right after the first
         # backward GEMMs) and the conv variables (ready last).  With >1 rank bucket 0 is reduced + updated on its own
@@ -174,7 +178,7 @@ class NativeEngine:
     def _forward(self, x, labels, *, training: bool, state, count=None) -> None:
         # early-weights PDL mode: in this schedule no kernel that stages weights before its dependency wait (conv2_fwd,
         # conv2_dgrad, head_forward) directly follows a kernel that writes weights
-        with native.pdl_mode(2):
+        with native.pdl_mode(self._pdl):
             self._forward_impl(x, labels, training=training, state=state, count=count)
 
     def _forward_impl(self, x, labels, *, training: bool, state, count=None) -> None:
@@ -213,7 +217,7 @@ class NativeEngine:
             count[0] += n
 
     def _backward(self, x, count, with_comm: bool = True) -> None:
-        with native.pdl_mode(2):
+        with native.pdl_mode(self._pdl):
             self._backward_impl(x, count, with_comm)
 
     def _backward_impl(self, x, count, with_comm: bool = True) -> None:
@@ -254,10 +258,23 @@ class NativeEngine:
             if self._on("dW3"):
                 native.gemm_bf16(self.p2, 1, dy1, 1, f.gradient("local3/weights"), 3136, s.fc1, B); n += 1
             self._fork_ev[1].record(self._side)
+        # without LRN the max-pool backward of conv2 rides in the epilogue of this GEMM (one N tile = one pooled pixel)
+        fused_unpool = not s.lrn and self._on("fused_unpool")
         if self._on("dP2"):
-            native.gemm_bf16(dy1, 0, f.weight_bf16("local3/weights"), 0, self.dp2, B, 3136, s.fc1,
-                             epilogue=native.EPI_MASK_BF16, ref=self.p2); n += 1
+            if fused_unpool:
+                native.gemm_mask_unpool(dy1, f.weight_bf16("local3/weights"), self.p2, self.arg2, self.dp2, self.dz2,
+                                        batch=B, hidden=s.fc1); n += 1
+            else:
+                native.gemm_bf16(dy1, 0, f.weight_bf16("local3/weights"), 0, self.dp2, B, 3136, s.fc1,
+                                 epilogue=native.EPI_MASK_BF16, ref=self.p2); n += 1
         self._mark("dP2_gemm")
+        if fused_unpool:
+            # conv2 bias gradient = column sums of dP2 over images and pooled pixels: beside the conv backward
+            self._fork_ev[8].record(main)
+            self._head_stream.wait_event(self._fork_ev[8])
+            with torch.cuda.stream(self._stream(self._head_stream)):
+                native.colsum_bf16(self.dp2.view(B * 49, 64), f.gradient("conv2/biases")); n += 1
+                self._fork_ev[9].record(self._head_stream)
         # bucket 0 (fc + head variables, 98 % of the elements): every gradient is complete once the dW GEMM is done and the
         # last reader of the fc weights (the dP2 GEMM above) has finished -> update it now, on its own stream, beside the
         # conv backward (tensor-core / latency bound kernels that leave the memory system idle).
@@ -278,7 +295,7 @@ class NativeEngine:
                                               finish=False, max_ctas=self._early_update_ctas)
                 n += 1
                 self._fork_ev[5].record(self._comm_stream)
-        if self._on("unpool2"):
+        if self._on("unpool2") and not fused_unpool:
             native.unpool2(self.dp2, self.arg2, self.act2, self.dz2, f.gradient("conv2/biases"), batch=B, lrn=s.lrn); n += 1
         self._mark("unpool2")
         # dgrad first: it and wgrad both need > 113 KB of shared memory and cannot share an SM, so launching them together
@@ -287,20 +304,24 @@ class NativeEngine:
             native.conv2_dgrad(self.dz2, f.weight_bf16("conv2/weights"), self.p1, self.pool_raw, self.dpool1, batch=B, lrn=s.lrn,
                                packed=self.w2_dgrad); n += 1
         self._mark("conv2_dgrad")
+        # conv2_wgrad is the longer of the two weight-gradient kernels: it stays on the main stream (programmatic edge from
+        # dgrad, no cross-stream hand-off on the critical path); conv1_wgrad (26 KB of smem, CUDA cores) co-resides with it
         self._fork_ev[2].record(main)
         self._side.wait_event(self._fork_ev[2])
         with torch.cuda.stream(self._stream(self._side)):
-            if self._on("conv2_wgrad"):
-                native.conv2_wgrad(self.p1, self.dz2, f.gradient("conv2/weights"), batch=B); n += 1
+            if self._on("conv1_wgrad"):
+                native.conv1_wgrad(x, self.dpool1, self.arg1, f.gradient("conv1/weights"), f.gradient("conv1/biases"),
+                                   channels=s.channels); n += 1
             self._fork_ev[3].record(self._side)
-        if self._on("conv1_wgrad"):
-            native.conv1_wgrad(x, self.dpool1, self.arg1, f.gradient("conv1/weights"), f.gradient("conv1/biases"),
-                               channels=s.channels); n += 1
+        if self._on("conv2_wgrad"):
+            native.conv2_wgrad(self.p1, self.dz2, f.gradient("conv2/weights"), batch=B); n += 1
         self._mark("conv1_wgrad")
         main.wait_event(self._fork_ev[1])
         main.wait_event(self._fork_ev[3])
         if self._on("head_bwd") and self._fuse_dh:
             main.wait_event(self._fork_ev[7])
+        if fused_unpool:
+            main.wait_event(self._fork_ev[9])
         self._mark("join_wgrad")
         if early_update:
             main.wait_event(self._fork_ev[5])

@@ -20,13 +20,14 @@
 extern "C" {
 #endif
 
-#define DTM_ABI_VERSION 6
+#define DTM_ABI_VERSION 7
 
 /* GEMM epilogues */
 #define DTM_EPI_STORE_F32 0      /* D(fp32)  = alpha * acc          (split-K: red.add into pre-zeroed D) */
 #define DTM_EPI_BIAS_BF16 1      /* D(bf16)  = acc + bias                                            */
 #define DTM_EPI_BIAS_RELU_BF16 2 /* D(bf16)  = dropout(relu(acc + bias))                              */
 #define DTM_EPI_MASK_BF16 3      /* D(bf16)  = acc * (ref > 0)      (ReLU backward)                   */
+#define DTM_EPI_MASK_UNPOOL_BF16 4 /* as 3, plus un-pooling into conv2's plane layout (dtm_gemm_mask_unpool only) */
 
 /* Optimizers (reference: tf_parameter_mgr.getOptimizer(lr), mnist_input.py:261) */
 #define DTM_OPT_SGD 0
@@ -119,6 +120,15 @@ int dtm_umma_probe(const void* image, uint32_t image_bytes, const void* ops, uin
 int dtm_gemm_bf16(const void* a, int a_mn_major, const void* b, int b_mn_major, void* d, int M, int N, int K,
                   int ldd, int epilogue, const float* bias, const void* ref, float alpha, float keep_prob,
                   uint64_t seed, const long long* step_ptr, int split_k, void* stream);
+
+/* Gradient GEMM of the first fully connected layer fused with the max-pool backward of conv2 (non-LRN presets):
+ *   dp2[B][3136] (bf16) = (dy[B][hidden] . w_bf16[3136][hidden]^T) * [p2 > 0]         (what DTM_EPI_MASK_BF16 computes)
+ *   dz2_planes (plane layout, 64 ch): every pooled value routed to its arg-max position, the other three positions of the
+ *   window zeroed - exactly what dtm_unpool2 writes.  One N tile of the GEMM is one pooled pixel (64 channels), so the
+ *   epilogue thread that owns an (image, pooled pixel) writes its 2x2 window directly.  The conv2 bias gradient (column sums
+ *   of dp2) is left to dtm_colsum_bf16, off the critical path. */
+int dtm_gemm_mask_unpool(const void* dy, const void* w_bf16, const void* p2, const void* argmax, void* dp2, void* dz2_planes,
+                         int batch, int hidden, void* stream);
 
 /* ---- conv1 (reference: mnist_input.py:39, :134-153) ----------------------------------------------------------- */
 /* x: uint8 [B][28*28*C] (in_is_float = 0, normalised x/255-0.5 in-kernel) or float32 already normalised.

@@ -180,6 +180,34 @@ def test_unpool2_and_conv2_backward(B):
     assert _rel_err(dw2.cpu(), want_dw) < 1e-3
 
 
+def test_gemm_mask_unpool_matches_gemm_plus_unpool():
+    """The fused dP2 GEMM epilogue writes the same dP2 and the same un-pooled planes as GEMM + unpool2 kernel."""
+    native, layouts = _native()
+    g = torch.Generator().manual_seed(23)
+    B, hidden = 200, 256
+    dy = (torch.randn(B, hidden, generator=g) * 0.1).to(torch.bfloat16).to(DEV)
+    w = (torch.randn(3136, hidden, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
+    p2 = torch.relu(torch.randn(B, 3136, generator=g)).to(torch.bfloat16).to(DEV)
+    arg = torch.randint(0, 4, (B, 49, 64), dtype=torch.uint8, generator=g).to(DEV)
+    dp2_a = torch.zeros(B, 3136, dtype=torch.bfloat16, device=DEV)
+    native.gemm_bf16(dy, 0, w, 0, dp2_a, B, 3136, hidden, epilogue=native.EPI_MASK_BF16, ref=p2)
+    planes_a = layouts.alloc_planes(B, 64, DEV)
+    db = torch.zeros(64, device=DEV)
+    native.unpool2(dp2_a, arg, None, planes_a, db, batch=B)
+    dp2_b = torch.zeros(B, 3136, dtype=torch.bfloat16, device=DEV)
+    planes_b = layouts.alloc_planes(B, 64, DEV)
+    native.gemm_mask_unpool(dy, w, p2, arg, dp2_b, planes_b, batch=B, hidden=hidden)
+    torch.cuda.synchronize()
+    assert torch.equal(dp2_a, dp2_b)
+    assert torch.equal(planes_a, planes_b)
+    assert layouts.planes_border_is_zero(planes_b, 64)
+    want = (dy.float() @ w.float().t()) * (p2.float() > 0)
+    assert _rel_err(dp2_b.float().cpu(), want.cpu()) < 1e-2
+    db2 = torch.zeros(64, device=DEV)
+    native.colsum_bf16(dp2_b.view(B * 49, 64), db2)
+    assert _rel_err(db2.cpu(), db.cpu()) < 1e-4
+
+
 def test_conv1_wgrad():
     native, _ = _native()
     g = torch.Generator().manual_seed(14)
