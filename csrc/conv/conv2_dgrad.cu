@@ -27,8 +27,11 @@ constexpr int DG_SMEM = DG_W_BYTES + PL_GUARD_BYTES + DG_BUFS * DG_IMG_BYTES + P
 // warps share each TMEM lane quadrant (16 of the 32 channels each); LRN backward needs all 32 channels in one thread.
 template <bool LRN> struct DgEpi { static constexpr int WARPS = LRN ? 4 : 8; static constexpr int CH = LRN ? 32 : 16; };
 
+// The non-LRN kernel declares 512 threads (it is launched with 384) to cap itself at 128 registers per thread: 384 x 128 =
+// 48 K registers leave room for a CTA of the optimizer-update kernel that runs beside the conv backward - at 165 registers
+// the two kernels could not share an SM and simply took turns.
 template <bool LRN>
-__global__ void __launch_bounds__(128 + 32 * DgEpi<LRN>::WARPS, 1)
+__global__ void __launch_bounds__(LRN ? 256 : 512, 1)
 conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* __restrict__ w2,
                    const uint8_t* __restrict__ w_packed, const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __restrict__ pool_raw, int batch,
                    __nv_bfloat16* __restrict__ dpool1, int early_weights) {

@@ -12,6 +12,8 @@ Step schedule (``baseline`` preset; ``reference`` adds LRN inside the conv kerne
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from ..models.params import FlatParams
@@ -53,6 +55,7 @@ class NativeEngine:
         self._side = torch.cuda.Stream(device=self.device)
         self._comm_stream = torch.cuda.Stream(device=self.device)
         self._head_stream = torch.cuda.Stream(device=self.device)
+        self._main_priority = -1 if os.environ.get("DTM_PRIORITY", "0") != "0" else 0
         # dH inside head_forward pays off while the head's weight rows fit one shared-memory staging chunk (1024 hidden units);
         # beyond that (the wide preset) the forward kernel would stage every chunk twice
         self._fuse_dh = (spec.fc2 or spec.fc1) <= 1024
@@ -72,7 +75,14 @@ class NativeEngine:
         import os as _os
         self._skip = set(filter(None, _os.environ.get("DTM_SKIP", "").split(",")))
         self._serial = _os.environ.get("DTM_SERIAL", "0") == "1"
-        self._early_update_ctas = int(_os.environ.get("DTM_EARLY_UPDATE_CTAS", "0"))
+        # grid cap of the early optimizer update: one CTA per SM.  conv2_dgrad (capped at 128 registers for this purpose) leaves
+        # room for exactly one update CTA per SM, so the two kernels really run side by side; an uncapped update grid floods
+        # the SMs first and dgrad has to wait for it to drain (measured: 179.6 -> 169.6 us per step)
+        sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
+        # (wide preset: the update itself is the long pole and needs every SM's load slots - no cap)
+        # (reference preset: its LRN backward kernels have a different footprint; the cap measured slower there, 406 -> 429 us)
+        small = self.flat.total <= (8 << 20) and not spec.lrn
+        self._early_update_ctas = int(_os.environ.get("DTM_EARLY_UPDATE_CTAS", str(sm_count if small else 0)))
         self.trace = None   # set to a list to collect (label, cuda event) marks on the main stream (tools/phase_times.py)
 
     # ------------------------------------------------------------------------------------------------
@@ -333,6 +343,8 @@ class NativeEngine:
         """Close the step: the conv bucket (bucket 0 was launched from inside the backward pass)."""
         f = self.flat
         lo, hi = self.buckets[1] if getattr(self, "_early_update_done", False) else (0, f.total)
+        if not self._on("update1"):
+            return
         if self.sharded:
             self.comm.fused_allreduce_update(self.cfg, self.state, f, lo, hi, finish=True)
         else:
@@ -369,7 +381,9 @@ class NativeEngine:
             torch.cuda.synchronize(self.device)
             self._restore(snap)
             g = torch.cuda.CUDAGraph()
-            cap = torch.cuda.Stream(device=self.device)
+            # the critical path (main stream) gets the higher priority: when its kernels and the side-stream kernels (dW3,
+            # conv1_wgrad, the early optimizer update) compete for SMs, the block scheduler serves the main chain first
+            cap = torch.cuda.Stream(device=self.device, priority=self._main_priority)
             cap.wait_stream(torch.cuda.current_stream())
             with torch.cuda.graph(g, stream=cap):
                 self._step_body(slot)

@@ -9,8 +9,8 @@ import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-KERNELS = ["conv1_fwd", "conv2_fwd", "fc1_fwd", "head_fwd", "head_bwd", "dW3", "dP2", "update0", "unpool2", "conv2_dgrad",
-           "conv2_wgrad", "conv1_wgrad"]
+KERNELS = ["conv1_fwd", "conv2_fwd", "fc1_fwd", "head_fwd", "head_bwd", "dW3", "dP2", "update0", "fused_unpool", "conv2_dgrad",
+           "conv2_wgrad", "conv1_wgrad", "update1"]
 
 
 def run_one(preset, batch, skip="", serial=False):
@@ -47,10 +47,10 @@ def main():
     args = ap.parse_args()
     base = run_one(args.preset, args.batch)
     serial = run_one(args.preset, args.batch, serial=True)
-    for ctas in (74, 148, 592, 0):
-        os.environ["DTM_EARLY_UPDATE_CTAS"] = str(ctas)
-        print(f"early-update grid cap {ctas}: {run_one(args.preset, args.batch):.1f} us", flush=True)
-    os.environ.pop("DTM_EARLY_UPDATE_CTAS", None)
+    for mode in ("0", "1"):
+        os.environ["DTM_PDL"] = mode
+        print(f"DTM_PDL={mode}: {run_one(args.preset, args.batch):.1f} us", flush=True)
+    os.environ.pop("DTM_PDL", None)
     out = {"full_step_us": base, "serial_step_us": serial, "marginal_us": {}}
     print(f"full step {base:.1f} us ; all kernels on one stream {serial:.1f} us", flush=True)
     for k in (args.only.split(",") if args.only else KERNELS):
