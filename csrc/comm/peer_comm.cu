@@ -156,7 +156,12 @@ DTM_DEVICE void shard_range(int lo, int hi, int rank, int world, int& s_lo, int&
 }
 
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(512, 1)
+// Two instantiations.  NVLS: 256 threads and at most 64 registers (launch bounds 256 x 4), one CTA per SM - small enough to
+// sit on an SM NEXT TO a conv-backward CTA (conv2_dgrad: 384 threads x 128 registers), so the gradient exchange of the fc
+// bucket really runs under the conv backward instead of taking SMs away from it; the in-switch reduction needs few loads in
+// flight (8-GPU sweep: 32 CTAs reach the same time as 148).  P2P: 512 threads, N-1 peer loads in flight per thread.
+template <bool NVLS>
+__global__ void __launch_bounds__(NVLS ? 256 : 512, NVLS ? 4 : 1)
 fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cfg, dtm_train_state* __restrict__ st,
                               int lo, int hi, float* __restrict__ slot0, float* __restrict__ slot1,
                               float* __restrict__ ema, __nv_bfloat16* __restrict__ w_bf16, CommCtrl* __restrict__ ctrl,
@@ -209,7 +214,7 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   // ---- reduce-scatter + optimizer on my shard + all-gather of the new weights
   int s_lo, s_hi;
   shard_range(lo, hi, r, N, s_lo, s_hi);
-  const bool nvls = ctx.mc_grad != nullptr && ctx.mc_w != nullptr && ctx.mc_w_bf16 != nullptr;
+  constexpr bool nvls = NVLS;
   int seg = 0;
   // optimizer + EMA on one float4 of my shard, then publish it: multicast store (NVLS) or N-1 peer stores (P2P)
   auto apply = [&](int i, const float4 g) {
@@ -242,8 +247,9 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   };
   const int step = nthreads * 4;
   if (nvls) {
-    // `depth` (<= 8) in-switch reductions in flight per thread before the first one is consumed
-    constexpr int U = 8;
+    // `depth` (<= 2) in-switch reductions in flight per thread before the first one is consumed
+    constexpr int U = 2;
+    depth = depth > U ? U : depth;
     for (int base = s_lo + tid * 4; base < s_hi; base += step * depth) {
       float4 g[U];
 #pragma unroll
@@ -398,9 +404,9 @@ static int launch_cooperative(Kernel kern, int grid, int block, cudaStream_t s, 
   return 0;
 }
 
-static int comm_grid(size_t elems, int max_ctas = 0) {
+static int comm_grid(size_t elems, int max_ctas = 0, int threads = 512) {
   // enough CTAs to keep 18 NVLinks busy, never more than one per SM (co-residency for the spin barriers)
-  size_t want = (elems / 4 + 511) / 512;
+  size_t want = (elems / 4 + threads - 1) / threads;
   int cap = device_sm_count();
   if (max_ctas > 0 && max_ctas < cap) cap = max_ctas;
   if (want < 1) want = 1;
@@ -411,7 +417,7 @@ static int comm_grid(size_t elems, int max_ctas = 0) {
 static int comm_depth() {
   const char* e = getenv("DTM_COMM_DEPTH");   // read per launch (cheap) so that tools can sweep it inside one process
   const int v = e ? atoi(e) : 2;   // 8-GPU sweep (profiles/fused_exchange_8gpu_sweep_r1.json): 1-2 best, 8 worst
-  return v < 1 ? 1 : (v > 8 ? 8 : v);
+  return v < 1 ? 1 : (v > 2 ? 2 : v);
 }
 
 static int check_ctx(const dtm_peer_ctx* ctx) {
@@ -465,7 +471,12 @@ extern "C" int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_upd
   if (lo < 0 || hi > cfg->total || lo >= hi || lo % 64 || hi % 64) return dtm_fail("fused_allreduce_update: bad element range");
   if (cfg->optimizer == DTM_OPT_ADAM && (!slot0 || !slot1)) return dtm_fail("fused_allreduce_update: Adam needs both slots");
   if (cfg->optimizer == DTM_OPT_MOMENTUM && !slot0) return dtm_fail("fused_allreduce_update: Momentum needs slot0");
-  return launch_cooperative(fused_allreduce_update_kernel, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
+  const bool nvls = ctx->mc_grad != nullptr && ctx->mc_w != nullptr && ctx->mc_w_bf16 != nullptr;
+  if (nvls)
+    return launch_cooperative(fused_allreduce_update_kernel<true>, comm_grid(static_cast<size_t>(hi - lo), max_ctas, 256), 256,
+                              static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
+                              static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
+  return launch_cooperative(fused_allreduce_update_kernel<false>, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
                             static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
                             static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
 }

@@ -139,14 +139,19 @@ def _nvls_available(group, device) -> bool:
 
 
 class PeerComm:
-    def __init__(self, group, device, *, overlap_ctas: int = 64):
+    def __init__(self, group, device, *, overlap_ctas: int | None = None):
         self.group, self.device = group, torch.device(device)
         self.rank, self.world_size = dist.get_rank(group), dist.get_world_size(group)
         if self.world_size > MAX_RANKS:
             raise ValueError(f"PeerComm supports up to {MAX_RANKS} ranks on one NVSwitch node")
         torch.cuda.set_device(self.device)
-        self.overlap_ctas = overlap_ctas
         self.nvls = _nvls_available(group, self.device)   # in-switch reduction + multicast stores (multimem.*)
+        # grid cap of a fused exchange that overlaps compute kernels.  NVLS kernel: 0 = one small CTA on every SM, co-resident
+        # with the conv backward (2 GPUs: 222 -> 189 us per step against a 64-CTA cap); P2P kernel (512 threads, cannot
+        # share an SM with conv2_dgrad): 64 CTAs.
+        if overlap_ctas is None:
+            overlap_ctas = 0 if self.nvls else 64
+        self.overlap_ctas = int(os.environ.get("DTM_OVERLAP_CTAS", overlap_ctas))
         self.use_multicast = self.nvls                    # the fused update takes the NVLS path (A/B switch for tools)
         self._buffers: list[SymmetricBuffer] = []
         self.flags = self._alloc(MAX_RANKS * 4 * 16)          # epochs, padded
