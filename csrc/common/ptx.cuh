@@ -21,6 +21,29 @@ DTM_DEVICE uint32_t lane_id() {
   return l;
 }
 
+// ---- thread-block clusters / distributed shared memory ------------------------------------------------------------
+DTM_DEVICE uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// Barrier over every thread of the cluster (non-aligned form: warps whose lanes diverged may call it lane by lane).
+// Release/acquire: shared-memory writes made before it - including writes into a peer CTA's shared memory - are visible
+// to every thread of the cluster after it.
+DTM_DEVICE void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
+}
+// Address of `local_smem_addr` (a shared::cta address of this CTA's window) in CTA `rank` of the cluster.
+DTM_DEVICE uint32_t cluster_map_shared(uint32_t local_smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+  return r;
+}
+DTM_DEVICE void st_shared_cluster_v4(uint32_t cluster_addr, float a, float b, float c, float d) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(cluster_addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 // Programmatic dependent launch (PDL).  A kernel launched with the programmatic-stream-serialization attribute may start
 // while its predecessor in the stream is still running; everything it does before pdl_wait() must be independent of the
 // predecessor's output (barrier init, TMEM allocation, staging of weights that were written at least two kernels

@@ -43,6 +43,10 @@ struct GemmArgs {
   // kernels consume - the separate un-pooling kernel and its launch gap disappear from the step's critical path
   const uint8_t* argmax;        // [M][49][64]
   uint8_t* planes;              // [M] plane-layout images, 64 channels
+  // Cluster split-K: the two CTAs of a (1,1,2) cluster each accumulate half of K for the SAME output tile; CTA 1 ships its
+  // fp32 partial tile into CTA 0's shared memory (DSMEM), CTA 0 adds it and runs the fused epilogue.  Doubles the number
+  // of SMs streaming operands when the tile count is below half the machine (the fc forward: 64 tiles, K = 3136).
+  int cluster_reduce;
 };
 
 // STAGES = 4: two CTAs per SM (grids larger than the machine, short K).  STAGES = 8: one CTA per SM with twice the
@@ -150,6 +154,32 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       mbar_wait(&accum_bar, 0, 3);
       tc_fence_after();
     }
+    // partial tile in CTA 0's (idle) stage memory: float4 (c/4, row) at ((c/4) * 128 + row) * 16 - consecutive rows are
+    // consecutive 16-byte words, so neither the remote stores nor the loads below conflict
+    const uint32_t part_row = smem_u32(smem_a) + (q * 32 + lane_id()) * 16;
+    if (g.cluster_reduce) {
+      cluster_sync();   // #1: both CTAs have finished their MMAs - CTA 0's stage buffers are free
+      if (blockIdx.z == 1) {
+        const uint32_t dst = cluster_map_shared(part_row, 0);
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t r[32];
+          if (num_kb > 0) {
+            tmem_ld_x32(tmem_d + ((q * 32u) << 16) + c, r);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = 0;
+          }
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            st_shared_cluster_v4(dst + ((c + j) >> 2) * (BM * 16), __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                                 __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+        }
+      }
+      cluster_sync();   // #2: the partial tile has landed in CTA 0
+    }
+    if (!g.cluster_reduce || blockIdx.z == 0) {
     long long step = 0;
     if (g.epilogue == DTM_EPI_BIAS_RELU_BF16 && g.keep_prob < 1.0f && g.step_ptr) step = *g.step_ptr;
     const uint32_t keep_thresh = static_cast<uint32_t>(g.keep_prob * 16777216.0f);
@@ -165,12 +195,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
         for (int j = 0; j < 32; ++j) r[j] = 0;
       }
+      if (g.cluster_reduce) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          float4 p;
+          asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(p.x), "=f"(p.y), "=f"(p.z), "=f"(p.w)
+                       : "r"(part_row + ((c + j) >> 2) * (BM * 16)));
+          r[j] = __float_as_uint(__uint_as_float(r[j]) + p.x);
+          r[j + 1] = __float_as_uint(__uint_as_float(r[j + 1]) + p.y);
+          r[j + 2] = __float_as_uint(__uint_as_float(r[j + 2]) + p.z);
+          r[j + 3] = __float_as_uint(__uint_as_float(r[j + 3]) + p.w);
+        }
+      }
       const int n = n0 + c;
       if (m >= g.M || n >= g.N) continue;
       const int valid = min(32, g.N - n);  // N % 8 == 0 is enforced by the host wrapper
       if (g.epilogue == DTM_EPI_STORE_F32) {
         float* out = static_cast<float*>(g.d) + static_cast<size_t>(m) * g.ldd + n;
-        if (gridDim.z > 1) {
+        if (gridDim.z > 1 && !g.cluster_reduce) {
           for (int j = 0; j < valid; j += 4)
             red_add_v4_f32(out + j, g.alpha * __uint_as_float(r[j]), g.alpha * __uint_as_float(r[j + 1]),
                            g.alpha * __uint_as_float(r[j + 2]), g.alpha * __uint_as_float(r[j + 3]));
@@ -250,6 +292,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
       }
     }
+    }   // CTA 0 of a cluster / every CTA without cluster split
+  }
+  if (warp < 4 && g.cluster_reduce) {   // the cluster barrier counts every thread of both CTAs
+    __syncwarp();
+    cluster_sync();
+    cluster_sync();
   }
 
   tc_fence_before();
@@ -265,7 +313,7 @@ static int launch_gemm_s(const CUtensorMap& ta, const CUtensorMap& tb, const Gem
     DTM_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(STAGES)));
     configured = true;
   }
-  DTM_CUDA_OK(launch_pdl(kern, grid, dim3(256), gemm_smem_bytes(STAGES), s, ta, tb, g));
+  DTM_CUDA_OK(launch_pdl_cluster(kern, grid, dim3(256), gemm_smem_bytes(STAGES), s, g.cluster_reduce ? 2 : 1, ta, tb, g));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -297,6 +345,14 @@ static int gemm_run(const void* a, int a_mn_major, const void* b, int b_mn_major
   int splits = split_k < 1 ? 1 : split_k;
   if (splits > total_kb) splits = total_kb;
   if (splits > 1 && epilogue != DTM_EPI_STORE_F32) return dtm_fail("gemm: split-K requires the fp32 store epilogue");
+  // bf16 epilogues with few tiles and a deep K: split K over the two CTAs of a cluster (reduction through DSMEM).
+  // Opt-in (DTM_GEMM_CLUSTER=1): measured on the fc forward (64 tiles, K = 3136) the kernel alone gains 17.0 -> 15.7 us,
+  // but inside the training step's programmatic-launch chain the cluster launch costs more than that (170.6 -> 180.3 us
+  // per step), so the engine leaves it off.
+  const int tiles_mn = ((N + BN - 1) / BN) * ((M + BM - 1) / BM);
+  const bool cluster_reduce = splits == 1 && epilogue != DTM_EPI_STORE_F32 && 2 * tiles_mn <= device_sm_count() && total_kb >= 16 &&
+                              (getenv("DTM_GEMM_CLUSTER") && getenv("DTM_GEMM_CLUSTER")[0] == '1');
+  if (cluster_reduce) splits = 2;
   const int per = (total_kb + splits - 1) / splits;
   splits = (total_kb + per - 1) / per;
 
@@ -321,6 +377,7 @@ static int gemm_run(const void* a, int a_mn_major, const void* b, int b_mn_major
   g.keep_prob = keep_prob;
   g.seed = seed;
   g.step_ptr = step_ptr;
+  g.cluster_reduce = (cluster_reduce && splits == 2) ? 1 : 0;
   g.argmax = static_cast<const uint8_t*>(argmax);
   g.planes = static_cast<uint8_t*>(planes);
   cudaStream_t s = static_cast<cudaStream_t>(stream);

@@ -81,6 +81,35 @@ def test_gemm_bias_relu_dropout_and_mask():
     assert _rel_err(d2.cpu(), want2) < 1e-2
 
 
+@pytest.mark.parametrize("M,N,K,b_mn", [(512, 1024, 3136, 1), (200, 192, 1024, 1), (320, 448, 2048, 0)])
+def test_gemm_cluster_split_k(M, N, K, b_mn):
+    """Few output tiles + deep K: the GEMM splits K over the two CTAs of a cluster and reduces through DSMEM.  Same result
+    as the un-split kernel up to fp32 summation order, and correct against fp32 matmul.  (Opt-in path: DTM_GEMM_CLUSTER=1.)"""
+    import os
+    native, _ = _native()
+    g = torch.Generator().manual_seed(M + K)
+    A = torch.randn(M, K, generator=g).to(torch.bfloat16)
+    B = (torch.randn(K, N, generator=g) * 0.05).to(torch.bfloat16)
+    bias = torch.randn(N, generator=g)
+    b = (B if b_mn else B.t().contiguous()).to(DEV)
+    d0 = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    native.gemm_bf16(A.to(DEV), 0, b, b_mn, d0, M, N, K, epilogue=native.EPI_BIAS_RELU_BF16, bias=bias.to(DEV))
+    ref = torch.randn(M, N, generator=g).to(torch.bfloat16)
+    os.environ["DTM_GEMM_CLUSTER"] = "1"     # opt-in switch of the cluster path (read per launch)
+    try:
+        d = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+        native.gemm_bf16(A.to(DEV), 0, b, b_mn, d, M, N, K, epilogue=native.EPI_BIAS_RELU_BF16, bias=bias.to(DEV))
+        d2 = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+        native.gemm_bf16(A.to(DEV), 0, b, b_mn, d2, M, N, K, epilogue=native.EPI_MASK_BF16, ref=ref.to(DEV))
+        torch.cuda.synchronize()
+    finally:
+        del os.environ["DTM_GEMM_CLUSTER"]
+    want = torch.relu(A.float() @ B.float() + bias)
+    assert _rel_err(d.cpu(), want) < 1e-2
+    assert _rel_err(d.float().cpu(), d0.float().cpu()) < 1e-2
+    assert _rel_err(d2.cpu(), (A.float() @ B.float()) * (ref.float() > 0)) < 1e-2
+
+
 # ----------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("channels,lrn", [(1, False), (3, True)])
 def test_conv1_forward(channels, lrn):
