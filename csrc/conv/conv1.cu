@@ -3,6 +3,7 @@
 // Weight gradient (autodiff of the same lines; conv1 has no input gradient): the pooled gradient is routed
 // through the saved arg-max to one of four positions, so each (pooled pixel, channel) contributes exactly one
 // 5x5 input patch; lanes keep the 25*C_in partial sums of their channel in registers.
+#include <stdlib.h>
 #include "../common/ptx.cuh"
 #include "../common/host_util.h"
 #include "../../include/dtm_b200.h"
@@ -110,13 +111,16 @@ extern "C" int dtm_conv1_wgrad(const void* x, int in_is_float, int channels, con
   using namespace dtm;
   if (channels != 1 && channels != 3) return dtm_fail("conv1_wgrad: channels must be 1 or 3");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const int grid = min(batch, 4 * device_sm_count());   // 3-4 CTAs per SM: the loop is LDS/FMA latency bound
+  // Every CTA ends with 26*C_in*32 red.add into the same few cache lines, so the CTA count sets the length of that serialised
+  // tail (512 single-image CTAs: ~16 K atomics per line, most of the kernel's time); a persistent grid of a couple of CTAs
+  // per SM keeps enough warps for the latency-bound main loop and cuts the atomics by the number of images per CTA.
+  const char* e = getenv("DTM_C1W_CTAS_PER_SM");
+  const int per_sm = e ? max(1, atoi(e)) : 2;
+  const int grid = min(batch, per_sm * device_sm_count());
   const __nv_bfloat16* g = static_cast<const __nv_bfloat16*>(grad_pooled);
   const uint8_t* a = static_cast<const uint8_t*>(argmax);
-  // plain launches: in the training schedule this kernel sits on a side stream behind an event (it joins that stream's
-  // own history with dgrad's), and a programmatic edge is only defined towards a single predecessor
-  if (channels == 1) conv1_wgrad_kernel<1><<<grid, 256, 0, s>>>(x, in_is_float, g, a, batch, dw, db);
-  else               conv1_wgrad_kernel<3><<<grid, 256, 0, s>>>(x, in_is_float, g, a, batch, dw, db);
+  if (channels == 1) DTM_CUDA_OK(launch_pdl(conv1_wgrad_kernel<1>, dim3(grid), dim3(256), 0, s, x, in_is_float, g, a, batch, dw, db));
+  else               DTM_CUDA_OK(launch_pdl(conv1_wgrad_kernel<3>, dim3(grid), dim3(256), 0, s, x, in_is_float, g, a, batch, dw, db));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -241,15 +241,7 @@ class NativeEngine:
                                  f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
                                  f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep); n += 1
         elif self._on("head_bwd"):
-            # third branch: dH already exists (head_forward), the head's own gradients run beside the fc GEMMs
-            self._fork_ev[6].record(main)
-            self._head_stream.wait_event(self._fork_ev[6])
-            with torch.cuda.stream(self._stream(self._head_stream)):
-                native.head_backward(h, f.weight("softmax_linear/weights"), self.dlogits, self.dh_last,
-                                     f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
-                                     f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep,
-                                     dh_ready=True); n += 1
-                self._fork_ev[7].record(self._head_stream)
+            self._fork_ev[6].record(main)   # the head's own gradients depend on head_forward only; launched further down
         self._mark("head_bwd")
         if s.fc2:
             # dW4 = h1^T . dY2 ; dY1 = (dY2 . W4^T) * [h1 > 0] ; db3 = colsum(dY1)
@@ -261,13 +253,11 @@ class NativeEngine:
         else:
             dy1 = self.dh_last
         lo0, hi0 = self.buckets[0]
-        # fork: the two big fc GEMMs are independent
+        # Three independent branches hang off this point: dP2 (feeds the whole conv backward: critical), dW3 and the head's
+        # weight/bias gradients (both only feed the optimizer).  Captured as dP2, head, dW3 - the block scheduler serves concurrently
+        # runnable kernels oldest first: with dW3 ahead of it dP2 started 10 us late, with the (light) head kernel last the
+        # optimizer update that waits for it started 14 us late (tools/timeline.py).
         self._fork_ev[0].record(main)
-        self._side.wait_event(self._fork_ev[0])
-        with torch.cuda.stream(self._stream(self._side)):
-            if self._on("dW3"):
-                native.gemm_bf16(self.p2, 1, dy1, 1, f.gradient("local3/weights"), 3136, s.fc1, B); n += 1
-            self._fork_ev[1].record(self._side)
         # without LRN the max-pool backward of conv2 rides in the epilogue of this GEMM (one N tile = one pooled pixel)
         fused_unpool = not s.lrn and self._on("fused_unpool")
         if self._on("dP2"):
@@ -277,6 +267,19 @@ class NativeEngine:
             else:
                 native.gemm_bf16(dy1, 0, f.weight_bf16("local3/weights"), 0, self.dp2, B, 3136, s.fc1,
                                  epilogue=native.EPI_MASK_BF16, ref=self.p2); n += 1
+        if self._on("head_bwd") and self._fuse_dh:
+            self._head_stream.wait_event(self._fork_ev[6])
+            with torch.cuda.stream(self._stream(self._head_stream)):
+                native.head_backward(h, f.weight("softmax_linear/weights"), self.dlogits, self.dh_last,
+                                     f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
+                                     f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep,
+                                     dh_ready=True); n += 1
+                self._fork_ev[7].record(self._head_stream)
+        self._side.wait_event(self._fork_ev[0])
+        with torch.cuda.stream(self._stream(self._side)):
+            if self._on("dW3"):
+                native.gemm_bf16(self.p2, 1, dy1, 1, f.gradient("local3/weights"), 3136, s.fc1, B); n += 1
+            self._fork_ev[1].record(self._side)
         self._mark("dP2_gemm")
         if fused_unpool:
             # conv2 bias gradient = column sums of dP2 over images and pooled pixels: beside the conv backward
