@@ -1,4 +1,5 @@
-// conv1 weight gradient on CUDA cores (the forward pass lives in conv1_tc.cu, on the tensor cores).
+// conv1 weight gradient on CUDA cores (default; conv1_wgrad_tc.cu is the opt-in tensor-core variant, the forward pass lives
+// in conv1_tc.cu).
 //
 // Weight gradient (autodiff of the same lines; conv1 has no input gradient): the pooled gradient is routed
 // through the saved arg-max to one of four positions, so each (pooled pixel, channel) contributes exactly one
@@ -106,9 +107,19 @@ conv1_wgrad_kernel(const void* __restrict__ x, int in_is_float, const __nv_bfloa
 
 }  // namespace dtm
 
+extern "C" int dtm_conv1_wgrad_tc(const void* x, int in_is_float, int channels, const void* grad_pooled, const void* argmax,
+                                  int batch, float* dw, float* db, void* stream);
+
 extern "C" int dtm_conv1_wgrad(const void* x, int in_is_float, int channels, const void* grad_pooled, const void* argmax,
                                int batch, float* dw, float* db, void* stream) {
   using namespace dtm;
+  // DTM_C1W_TC=1 selects the tensor-core kernel (conv1_wgrad_tc.cu).  It is correct and needs 1.7x fewer instructions, but
+  // as measured in round 1 it is slower than this kernel (41 vs 29 us alone, 60 vs 44 us beside conv2_wgrad: its producers
+  // wait on per-row global loads, and conv2_wgrad's 512-column TMEM allocation keeps it off the SM) - so it is opt-in.
+  {
+    const char* e = getenv("DTM_C1W_TC");
+    if (e && e[0] == '1') return dtm_conv1_wgrad_tc(x, in_is_float, channels, grad_pooled, argmax, batch, dw, db, stream);
+  }
   if (channels != 1 && channels != 3) return dtm_fail("conv1_wgrad: channels must be 1 or 3");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // Every CTA ends with 26*C_in*32 red.add into the same few cache lines, so the CTA count sets the length of that serialised

@@ -237,10 +237,13 @@ def test_gemm_mask_unpool_matches_gemm_plus_unpool():
     assert _rel_err(db2.cpu(), db.cpu()) < 1e-4
 
 
-def test_conv1_wgrad():
+@pytest.mark.parametrize("B,C,tc", [(41, 1, True), (600, 1, True), (41, 3, True), (41, 1, False), (41, 3, False)])
+def test_conv1_wgrad(B, C, tc):
+    """tc=True: the opt-in tensor-core kernel (bf16 operands, so the oracle rounds the normalised pixels to bf16 as well);
+    tc=False: the default CUDA-core kernel (fp32 pixels).  600 images: several work units per persistent CTA."""
+    import os
     native, _ = _native()
     g = torch.Generator().manual_seed(14)
-    B, C = 41, 1
     x = torch.randint(0, 256, (B, 784 * C), dtype=torch.uint8, generator=g)
     gp = _bf(torch.randn(B, 196, 32, generator=g) * (torch.rand(B, 196, 32, generator=g) > 0.5))
     arg = torch.randint(0, 4, (B, 196, 32), dtype=torch.uint8, generator=g)
@@ -249,12 +252,20 @@ def test_conv1_wgrad():
     for d in range(4):
         dz[:, :, d >> 1, :, d & 1, :] = torch.where(a == d, gp.view(B, 14, 14, 32), torch.zeros(()))
     dz = dz.view(B, 28, 28, 32).permute(0, 3, 1, 2)
-    xin = (x.float() / 255 - 0.5).view(B, 28, 28, C).permute(0, 3, 1, 2)
+    xin = (x.float() / 255 - 0.5)
+    if tc:
+        xin = _bf(x.float() * (1.0 / 255) - 0.5)
+    xin = xin.view(B, 28, 28, C).permute(0, 3, 1, 2)
     wv = torch.zeros(32, C, 5, 5, requires_grad=True)
     F.conv2d(xin, wv, None, padding=2).backward(dz)
     dw = torch.zeros(5, 5, C, 32, device=DEV)
     db = torch.zeros(32, device=DEV)
-    native.conv1_wgrad(x.to(DEV), gp.to(torch.bfloat16).to(DEV), arg.to(DEV), dw, db, channels=C)
+    os.environ["DTM_C1W_TC"] = "1" if tc else "0"
+    try:
+        native.conv1_wgrad(x.to(DEV), gp.to(torch.bfloat16).to(DEV), arg.to(DEV), dw, db, channels=C)
+        torch.cuda.synchronize()
+    finally:
+        os.environ.pop("DTM_C1W_TC", None)
     assert _rel_err(dw.cpu(), wv.grad.permute(2, 3, 1, 0)) < 1e-4
     assert _rel_err(db.cpu(), dz.sum(dim=(0, 2, 3))) < 1e-4
 
