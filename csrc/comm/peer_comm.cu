@@ -160,8 +160,10 @@ DTM_DEVICE void shard_range(int lo, int hi, int rank, int world, int& s_lo, int&
 // sit on an SM NEXT TO a conv-backward CTA (conv2_dgrad: 384 threads x 128 registers), so the gradient exchange of the fc
 // bucket really runs under the conv backward instead of taking SMs away from it; the in-switch reduction needs few loads in
 // flight (8-GPU sweep: 32 CTAs reach the same time as 148).  P2P: 512 threads, N-1 peer loads in flight per thread.
-template <bool NVLS>
-__global__ void __launch_bounds__(NVLS ? 256 : 512, NVLS ? 4 : 1)
+// (NVLS with LIGHT = false: 512 threads and four reductions in flight per thread - for shards of millions of elements,
+// where the rank-local optimizer traffic needs the memory parallelism: wide preset, 2 GPUs: 741 -> ~600 us per step.)
+template <bool NVLS, bool LIGHT>
+__global__ void __launch_bounds__(LIGHT ? 256 : 512, LIGHT ? 4 : 1)
 fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cfg, dtm_train_state* __restrict__ st,
                               int lo, int hi, float* __restrict__ slot0, float* __restrict__ slot1,
                               float* __restrict__ ema, __nv_bfloat16* __restrict__ w_bf16, CommCtrl* __restrict__ ctrl,
@@ -247,9 +249,9 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   };
   const int step = nthreads * 4;
   if (nvls) {
-    // `depth` (<= 2) in-switch reductions in flight per thread before the first one is consumed
-    constexpr int U = 2;
-    depth = depth > U ? U : depth;
+    // `depth` (<= U) in-switch reductions in flight per thread before the first one is consumed
+    constexpr int U = LIGHT ? 2 : 4;
+    depth = LIGHT ? (depth > U ? U : depth) : U;
     for (int base = s_lo + tid * 4; base < s_hi; base += step * depth) {
       float4 g[U];
 #pragma unroll
@@ -472,11 +474,17 @@ extern "C" int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_upd
   if (cfg->optimizer == DTM_OPT_ADAM && (!slot0 || !slot1)) return dtm_fail("fused_allreduce_update: Adam needs both slots");
   if (cfg->optimizer == DTM_OPT_MOMENTUM && !slot0) return dtm_fail("fused_allreduce_update: Momentum needs slot0");
   const bool nvls = ctx->mc_grad != nullptr && ctx->mc_w != nullptr && ctx->mc_w_bf16 != nullptr;
-  if (nvls)
-    return launch_cooperative(fused_allreduce_update_kernel<true>, comm_grid(static_cast<size_t>(hi - lo), max_ctas, 256), 256,
+  // light variant while a rank's shard stays below 2 M elements (every preset but `wide`)
+  const bool light = static_cast<size_t>(hi - lo) / ctx->world <= (2u << 20);
+  if (nvls && light)
+    return launch_cooperative(fused_allreduce_update_kernel<true, true>, comm_grid(static_cast<size_t>(hi - lo), max_ctas, 256), 256,
                               static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
                               static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
-  return launch_cooperative(fused_allreduce_update_kernel<false>, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
+  if (nvls)
+    return launch_cooperative(fused_allreduce_update_kernel<true, false>, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
+                              static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
+                              static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
+  return launch_cooperative(fused_allreduce_update_kernel<false, false>, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
                             static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
                             static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
 }

@@ -63,6 +63,10 @@ class NativeEngine:
         # gaps is worth 10 %.  With the wide preset the step is bound by dW3 -> optimizer update on the side streams; early-
         # resident CTAs of the main-stream chain then take SMs away from exactly those kernels (measured: 536 -> 562 us).
         self._pdl = 2 if self.flat.total <= (8 << 20) else 0
+        if comm is not None and self.flat.total > (8 << 20) and "DTM_OVERLAP_CTAS" not in os.environ:
+            # wide preset: the fc bucket's exchange runs ~200 us and is bound by the NVSwitch, not by the number of CTAs
+            # (8-GPU sweep: 32 CTAs reach the time of 148) - leave most SMs entirely to the conv backward
+            comm.overlap_ctas = 64
         self._fork_ev = [torch.cuda.Event() for _ in range(10)]
         # gradient buckets in flat-buffer order: the fc/head variables (93 % of the bytes, ready right after the first
         # backward GEMMs) and the conv variables (ready last).  With >1 rank bucket 0 is reduced + updated on its own
