@@ -29,17 +29,31 @@ class SyntheticMnist:
             images = np.clip(templates[labels] * 0.6 + 50.0 + noise, 0, 255).astype(np.uint8)
         else:
             images = rng.integers(0, 256, size=(pool_batches, batch_size, image_pixels), dtype=np.uint8)
-        self.images = torch.from_numpy(images)
-        self.labels = torch.from_numpy(labels)
+        # one packed buffer per batch (pixels | padding to 16 bytes | int32 labels): the feeder moves a batch with a single
+        # H2D copy; ``images`` / ``labels`` are views into it
+        nb = batch_size * image_pixels
+        pad = (-nb) % 16
+        self.label_offset = nb + pad
+        packed = np.zeros((pool_batches, nb + pad + 4 * batch_size), dtype=np.uint8)
+        packed[:, :nb] = images.reshape(pool_batches, nb)
+        packed[:, nb + pad:] = labels.view(np.uint8).reshape(pool_batches, 4 * batch_size)
+        self.packed = torch.from_numpy(packed)
         if pin and torch.cuda.is_available():
-            self.images = self.images.pin_memory()
-            self.labels = self.labels.pin_memory()
+            self.packed = self.packed.pin_memory()
+        self.images = self.packed[:, :nb].view(pool_batches, batch_size, image_pixels)
+        self.labels = self.packed[:, nb + pad:].view(torch.int32)
         self._cursor = 0
 
     def next(self) -> tuple[torch.Tensor, torch.Tensor]:
         i = self._cursor % self.pool_batches
         self._cursor += 1
         return self.images[i], self.labels[i]
+
+    def next_packed(self) -> torch.Tensor:
+        """The next batch as one contiguous buffer (see ``NativeEngine.stage_packed``)."""
+        i = self._cursor % self.pool_batches
+        self._cursor += 1
+        return self.packed[i]
 
     def __iter__(self):
         while True:
@@ -67,12 +81,18 @@ class DeviceFeeder:
         self._primed = False
         self._used: set[int] = set()
         self.h2d_bytes_per_step = engine.B * engine.spec.image_pixels + engine.B * 4
+        # packed sources (pixels + labels in one pinned buffer of the engine's slot layout) need one copy per batch
+        self._packed = (hasattr(source, "next_packed") and hasattr(engine, "stage_packed")
+                        and getattr(source, "label_offset", -1) == getattr(engine, "packed_label_offset", -2))
 
     def _issue_copy(self, slot: int) -> None:
-        images, labels = self.source.next()
         if slot in self._used:
             self.copy_stream.wait_event(self.free[slot])
-        self.engine.stage_batch(slot, images, labels, stream=self.copy_stream)
+        if self._packed:
+            self.engine.stage_packed(slot, self.source.next_packed(), stream=self.copy_stream)
+        else:
+            images, labels = self.source.next()
+            self.engine.stage_batch(slot, images, labels, stream=self.copy_stream)
         self.ready[slot].record(self.copy_stream)
 
     def step(self) -> None:

@@ -93,8 +93,13 @@ class NativeEngine:
     def _alloc_activations(self, keep_logits: bool) -> None:
         B, s, dev = self.B, self.spec, self.device
         z = lambda *shape, dtype: torch.zeros(*shape, dtype=dtype, device=dev)
-        self.x = [z(B, s.image_pixels, dtype=torch.uint8) for _ in range(2)]
-        self.y = [z(B, dtype=torch.int32) for _ in range(2)]
+        # one buffer per slot: pixels, then labels - a packed pinned host batch arrives with a single H2D copy
+        nb = B * s.image_pixels
+        pad = (-nb) % 16
+        self.xy = [z(nb + pad + 4 * B, dtype=torch.uint8) for _ in range(2)]
+        self.x = [b[:nb].view(B, s.image_pixels) for b in self.xy]
+        self.y = [b[nb + pad:].view(torch.int32) for b in self.xy]
+        self.packed_bytes, self.packed_label_offset = nb + pad + 4 * B, nb + pad
         self.xf = None  # float input staging for inference with pre-normalised images
         self.p1 = layouts.alloc_planes(B, 32, dev)
         self.arg1 = z(B, 196, 32, dtype=torch.uint8)
@@ -373,6 +378,11 @@ class NativeEngine:
             self.x[slot].copy_(images_u8.view(self.B, -1), non_blocking=True)
             self.y[slot].copy_(labels.view(self.B).to(torch.int32) if labels.dtype != torch.int32 else labels.view(self.B),
                                non_blocking=True)
+
+    def stage_packed(self, slot: int, packed_u8: torch.Tensor, stream=None) -> None:
+        """One asynchronous copy of a packed batch (``packed_bytes`` uint8: pixels, padding to 16 bytes, int32 labels)."""
+        with torch.cuda.stream(stream if stream is not None else torch.cuda.current_stream()):
+            self.xy[slot].copy_(packed_u8, non_blocking=True)
 
     def train_step(self, slot: int = 0) -> None:
         """Run one optimisation step on the batch staged in ``slot`` (asynchronous; no host sync)."""
