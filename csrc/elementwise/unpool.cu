@@ -147,8 +147,20 @@ colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, int M, int N, float* __r
   pdl_wait();
   pdl_launch_dependents();
   float acc = 0.0f;
-  if (n < N)
-    for (int m = blockIdx.y * 8 + r; m < M; m += gridDim.y * 8) acc += __bfloat162float(x[static_cast<size_t>(m) * N + n]);
+  if (n < N) {
+    // four independent loads per pass: with one the loop ran at a single L2 round trip per element (48 us for 3 MB)
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    const int step = gridDim.y * 8;
+    int m = blockIdx.y * 8 + r;
+    for (; m + 3 * step < M; m += 4 * step) {
+      a0 += __bfloat162float(x[static_cast<size_t>(m) * N + n]);
+      a1 += __bfloat162float(x[static_cast<size_t>(m + step) * N + n]);
+      a2 += __bfloat162float(x[static_cast<size_t>(m + 2 * step) * N + n]);
+      a3 += __bfloat162float(x[static_cast<size_t>(m + 3 * step) * N + n]);
+    }
+    for (; m < M; m += step) a0 += __bfloat162float(x[static_cast<size_t>(m) * N + n]);
+    acc = (a0 + a1) + (a2 + a3);
+  }
   s[r][threadIdx.x & 31] = acc;
   __syncthreads();
   if (r == 0 && n < N) {
@@ -186,7 +198,7 @@ extern "C" int dtm_colsum_bf16(const void* x, int M, int N, float* out, void* st
   using namespace dtm;
   if (M <= 0 || N <= 0) return dtm_fail("colsum: M and N must be positive");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  dim3 grid((N + 31) / 32, min(32, (M + 7) / 8));
+  dim3 grid((N + 31) / 32, min(2 * device_sm_count(), (M + 7) / 8));
   DTM_CUDA_OK(launch_pdl(colsum_bf16_kernel, grid, dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), M, N, out));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
