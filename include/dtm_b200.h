@@ -140,6 +140,10 @@ int dtm_conv1_fwd(const void* x, int in_is_float, int channels, const float* w, 
  * (red.add) and must be zero on entry. */
 int dtm_conv1_wgrad(const void* x, int in_is_float, int channels, const void* grad_pooled, const void* argmax, int batch,
                     float* dw, float* db, void* stream);
+/* Same contract on tcgen05 (K = pixels; bf16 operands, so pixels are rounded to bf16 after normalisation).  Verified, but
+ * slower than the CUDA-core kernel in round 1: dtm_conv1_wgrad only dispatches to it when DTM_C1W_TC=1. */
+int dtm_conv1_wgrad_tc(const void* x, int in_is_float, int channels, const void* grad_pooled, const void* argmax, int batch,
+                       float* dw, float* db, void* stream);
 
 /* ---- conv2 on tcgen05 (reference: mnist_input.py:156-172) ------------------------------------------------------ */
 /* w2_bf16: bf16 copy of the TF-layout weights [5][5][32][64].  p2: bf16 [B][7][7][64] (== [B][3136] in TF flatten
