@@ -18,6 +18,7 @@ import numpy as np
 import torch
 
 from ..formats import checkpoint_state as cs
+from ..formats import graph_def as gd
 from ..formats import tensor_bundle as tb
 from ..models.presets import ModelSpec
 
@@ -79,6 +80,30 @@ def collect_variables(engine, spec: ModelSpec, optimizer: str) -> dict[str, np.n
     return out
 
 
+def variable_inventory(spec: ModelSpec, optimizer: str) -> dict[str, tuple]:
+    """``name -> (dtype, shape)`` of everything :func:`collect_variables` returns, derived from the model spec alone (no
+    engine, no collective): what ``graph.pbtxt`` lists when the chief starts."""
+    out: dict[str, tuple] = {"global_step": (np.int64, ())}
+    for v in spec.variables:
+        out[v.name] = (np.float32, tuple(v.shape))
+    for v in spec.variables:
+        out[v.name + EMA_SUFFIX] = (np.float32, tuple(v.shape))
+    for slot_name in SLOT_NAMES[optimizer.lower()]:
+        for v in spec.variables:
+            out[f"{v.name}/{slot_name}"] = (np.float32, tuple(v.shape))
+    if optimizer.lower() == "adam":
+        out["beta1_power"] = (np.float32, ())
+        out["beta2_power"] = (np.float32, ())
+    for name, _ in loss_avg_names(spec):
+        out[name] = (np.float32, ())
+    return out
+
+
+def write_graph(train_dir: str, spec: ModelSpec, optimizer: str) -> str:
+    """``<train_dir>/graph.pbtxt`` — written once by the chief at session start, like MonitoredTrainingSession."""
+    return gd.write_graph_pbtxt(train_dir, variable_inventory(spec, optimizer))
+
+
 def shard_assignment(names: list[str], spec: ModelSpec, num_shards: int) -> dict[str, int]:
     """Round-robin placement over ps tasks in variable creation order (global_step first), like replica_device_setter."""
     if num_shards <= 1:
@@ -116,6 +141,7 @@ def save_checkpoint(train_dir: str, engine, spec: ModelSpec, optimizer: str, *, 
     if not write:
         return prefix
     tb.write_bundle(prefix, variables, shard_assignment(list(variables), spec, num_shards), num_shards)
+    gd.write_meta(prefix, gd.describe(variables), max_to_keep=max_to_keep, sharded=True)   # Saver(write_meta_graph=True)
     st = cs.read_state(train_dir) or cs.CheckpointState()
     rel = os.path.basename(prefix)
     paths = [p for p in st.all_model_checkpoint_paths if p != rel] + [rel]

@@ -73,6 +73,38 @@ class NanLossHook(Hook):
         self._check(loop)
 
 
+class StepCounterHook(Hook):
+    """``global_step/sec`` every ``every_n_steps`` global steps into the event file of ``train_dir`` itself — the default
+    ``StepCounterHook`` that ``MonitoredTrainingSession`` installs on the chief.  ``images/sec`` is
+    written next to it when the global batch size is known (the reference never reports throughput: main.py:149-154).
+    Host wall clock over asynchronous steps, i.e. the steady-state rate, like TensorFlow's hook."""
+
+    def __init__(self, writer, every_n_steps: int = 100, global_batch: int | None = None):
+        self.writer, self.every, self.global_batch = writer, max(1, every_n_steps), global_batch
+        self._t = self._step = None
+        self.last_rate = None
+
+    def begin(self, loop) -> None:
+        self._t, self._step = time.time(), loop.global_step
+
+    def after_run(self, ctx: RunContext) -> None:
+        from ..formats.events import scalar_value
+
+        gs = ctx.loop.global_step
+        if gs - self._step < self.every:
+            return
+        now = time.time()
+        rate = (gs - self._step) / max(now - self._t, 1e-9)
+        self.last_rate = rate
+        self.writer.add_summary(scalar_value("global_step/sec", rate), gs)
+        if self.global_batch:
+            self.writer.add_summary(scalar_value("images/sec", rate * self.global_batch), gs)
+        self._t, self._step = now, gs
+
+    def end(self, loop) -> None:
+        self.writer.flush()
+
+
 class LoggerHook(Hook):
     def __init__(self, monitor, writer, test_interval: int):
         self.monitor, self.writer, self.test_interval = monitor, writer, max(1, int(test_interval))

@@ -192,6 +192,9 @@ def train():
         saver = checkpointing.CheckpointSaver(FLAGS.train_dir, spec, opt.kind, save_secs=hp.save_checkpoint_secs,
                                               num_shards=max(1, cluster.num_ps), max_to_keep=hp.max_to_keep)
     if is_chief:
+        # what MonitoredTrainingSession does on the chief before the first step: graph.pbtxt + a step-rate counter
+        checkpointing.write_graph(FLAGS.train_dir, spec, opt.kind)
+        hooks.append(trainer.StepCounterHook(EventFileWriter(FLAGS.train_dir), 100, batch_size * max(1, role.world_size)))
         log_dir = os.path.join(FLAGS.train_dir, "log")
         monitor = monitor_cb.CMonitor(log_dir, test_interval, max_steps)
         writer = EventFileWriter(log_dir)

@@ -238,6 +238,14 @@ def test_checkpoint_inventory_resume_and_rotation(tmp_path):
     st = cs.read_state(d)
     assert st.model_checkpoint_path == "model.ckpt-7" and st.all_model_checkpoint_paths == [f"model.ckpt-{i}" for i in range(3, 8)]
     assert not os.path.exists(prefixes[0] + ".index") and os.path.exists(prefixes[-1] + ".index")
+    # every checkpoint carries a MetaGraphDef (Saver(write_meta_graph=True)); rotation removes it with the bundle
+    assert os.path.exists(prefixes[-1] + ".meta") and not os.path.exists(prefixes[0] + ".meta")
+    from tensorboard.compat.proto import meta_graph_pb2
+    mg = meta_graph_pb2.MetaGraphDef()
+    mg.ParseFromString(open(prefixes[-1] + ".meta", "rb").read())
+    assert {n.name for n in mg.graph_def.node} == expect and all(n.op == "VariableV2" for n in mg.graph_def.node)
+    assert mg.saver_def.version == 2 and mg.saver_def.sharded and mg.saver_def.max_to_keep == 5
+    assert set(ck.variable_inventory(spec, "adam")) == expect        # what graph.pbtxt lists, derived without an engine
     # resume into a fresh engine: bit-exact variables, optimizer state and step
     spec2, eng2 = _torch_engine("reference", B=4)
     assert ck.restore_checkpoint(d, eng2, spec2, "adam") == 7
@@ -284,6 +292,49 @@ def _write_idx(tmp, n=30):
         with open(os.path.join(tmp, fl), "wb") as f:
             f.write(struct.pack(">II", 2049, n) + labs.tobytes())
     return imgs, labs
+
+
+def test_graph_pbtxt_and_step_counter(tmp_path):
+    """The chief's session-start artefacts: graph.pbtxt parses as a GraphDef with the variable inventory, and
+    the step counter writes global_step/sec (+ images/sec) into the train_dir event file every N steps."""
+    from google.protobuf import text_format
+    from tensorboard.compat.proto import graph_pb2
+
+    from distributed_tensorflow_ibm_mnist_b200.formats import events, graph_def as gd
+    from distributed_tensorflow_ibm_mnist_b200.models import presets
+    from distributed_tensorflow_ibm_mnist_b200.train import checkpointing as ck, trainer
+
+    spec = presets.make_spec("baseline")
+    d = str(tmp_path / "train")
+    path = ck.write_graph(d, spec, "momentum")
+    g = graph_pb2.GraphDef()
+    text_format.Parse(open(path).read(), g)
+    inv = ck.variable_inventory(spec, "momentum")
+    assert [n.name for n in g.node] == list(inv)
+    node = {n.name: n for n in g.node}
+    assert [dim.size for dim in node["local3/weights/Momentum"].attr["shape"].shape.dim] == [3136, 1024]
+    assert node["global_step"].attr["dtype"].type == 9 and node["conv1/biases"].attr["dtype"].type == 1
+    g2 = graph_pb2.GraphDef()
+    g2.ParseFromString(gd.graph_def(inv))                       # binary encoder agrees with the text one
+    assert g2 == g
+
+    class _Loop:
+        global_step = 0
+
+    w = events.EventFileWriter(d)
+    hook = trainer.StepCounterHook(w, every_n_steps=5, global_batch=64)
+    loop = _Loop()
+    hook.begin(loop)
+    ctx = trainer.RunContext(loop)
+    for _ in range(12):
+        loop.global_step += 1
+        hook.after_run(ctx)
+    hook.end(loop)
+    w.close()
+    evs = [e for f in sorted(os.listdir(d)) if "tfevents" in f for e in events.read_events(os.path.join(d, f))]
+    tags = [(e["step"], tag) for e in evs for tag in e["scalars"]]
+    assert (5, "global_step/sec") in tags and (10, "global_step/sec") in tags and (10, "images/sec") in tags
+    assert not any(step == 12 for step, _ in tags) and hook.last_rate > 0
 
 
 def test_convert_mnist_idx_to_png_to_tfrecord_roundtrip(tmp_path):
