@@ -40,11 +40,94 @@ def parse_record(record: bytes, image_bytes: int | None = None) -> tuple[np.ndar
     return img, int(ex["label"])
 
 
+def _native_loader_lib():
+    """libdtm_b200.so if it is built (the loader is host code: no GPU needed), else None."""
+    try:
+        from ..ops import _lib
+        if not _lib.available():
+            return None
+        import ctypes
+        from ctypes import c_char_p, c_int, c_uint64, c_void_p, POINTER
+        _lib.register("dtm_loader_create", [POINTER(c_char_p), c_int, c_int, c_int, c_int, c_uint64, c_int, c_int], c_void_p)
+        _lib.register("dtm_loader_next", [c_void_p, c_void_p, c_void_p], c_int)
+        _lib.register("dtm_loader_records_read", [c_void_p], c_uint64)
+        _lib.register("dtm_loader_destroy", [c_void_p], None)
+        return _lib.load()
+    except Exception:  # noqa: BLE001 - no library, wrong ABI, ...: the Python pipeline below does the same job
+        return None
+
+
+class NativeRecordBatches:
+    """The same stream as :class:`TFRecordBatches`, produced by the C++ pipeline (csrc/io/record_loader.cpp): reader
+    threads, CRC checks, Example parsing and the shuffle queue run outside the interpreter, and a batch is written straight
+    into one packed buffer (pixels | padding | labels) that ``NativeEngine.stage_packed`` ships with a single H2D copy."""
+
+    def __init__(self, lib, filenames: list[str], batch_size: int, image_bytes: int, *, num_threads: int = 2, seed: int = 0,
+                 shuffle: bool = True, min_after_dequeue: int = MIN_AFTER_DEQUEUE, pin: bool = False):
+        import ctypes
+
+        self._lib = lib
+        self.filenames, self.B, self.image_bytes = list(filenames), batch_size, image_bytes
+        self.capacity = min_after_dequeue + 3 * batch_size
+        self.shuffle = shuffle
+        self.pin = pin and torch.cuda.is_available()
+        nb = batch_size * image_bytes
+        self.label_offset = nb + (-nb) % 16                       # NativeEngine's packed slot layout
+        self.packed_bytes = self.label_offset + 4 * batch_size
+        arr = (ctypes.c_char_p * len(filenames))(*[os.fsencode(f) for f in filenames])
+        self._h = lib.dtm_loader_create(arr, len(filenames), batch_size, image_bytes, num_threads, seed, int(shuffle),
+                                        min_after_dequeue)
+        if not self._h:
+            raise ValueError(lib.dtm_last_error().decode())
+
+    def next_packed(self) -> torch.Tensor:
+        buf = torch.empty(self.packed_bytes, dtype=torch.uint8, pin_memory=self.pin)
+        base = buf.data_ptr()
+        if self._lib.dtm_loader_next(self._h, base, base + self.label_offset) != 0:
+            raise ValueError(self._lib.dtm_last_error().decode())
+        return buf
+
+    def next(self) -> tuple[torch.Tensor, torch.Tensor]:
+        buf = self.next_packed()
+        return buf[:self.B * self.image_bytes].view(self.B, self.image_bytes), buf[self.label_offset:].view(torch.int32)
+
+    @property
+    def records_read(self) -> int:
+        return int(self._lib.dtm_loader_records_read(self._h)) if self._h else 0
+
+    def close(self) -> None:
+        if self._h:
+            self._lib.dtm_loader_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+
 class TFRecordBatches:
-    """Infinite stream of shuffled (uint8 [B, pixels], int32 [B]) batches read by background threads."""
+    """Infinite stream of shuffled (uint8 [B, pixels], int32 [B]) batches read by background threads.
+
+    ``TFRecordBatches(...)`` returns the native C++ pipeline (:class:`NativeRecordBatches`) when libdtm_b200.so is built;
+    ``native=False`` (or ``DTM_NATIVE_LOADER=0``) selects this pure-Python implementation, which is also the test oracle."""
+
+    def __new__(cls, filenames, batch_size, image_bytes, *, native: bool | None = None, **kw):
+        if native is None:
+            native = os.environ.get("DTM_NATIVE_LOADER", "1") != "0"
+        if native and cls is TFRecordBatches:
+            if not filenames:
+                raise ValueError("no input files")
+            check_files(list(filenames))
+            lib = _native_loader_lib()
+            if lib is not None:
+                return NativeRecordBatches(lib, list(filenames), batch_size, image_bytes, **kw)
+        return super().__new__(cls)
 
     def __init__(self, filenames: list[str], batch_size: int, image_bytes: int, *, num_threads: int = 2, seed: int = 0,
-                 shuffle: bool = True, min_after_dequeue: int = MIN_AFTER_DEQUEUE, pin: bool = False):
+                 shuffle: bool = True, min_after_dequeue: int = MIN_AFTER_DEQUEUE, pin: bool = False,
+                 native: bool | None = None):
         if not filenames:
             raise ValueError("no input files")
         check_files(filenames)
@@ -58,6 +141,8 @@ class TFRecordBatches:
         self._buf: list[tuple[np.ndarray, int]] = []
         self._stop = threading.Event()
         self._err: list[BaseException] = []
+        if not shuffle:
+            num_threads = 1          # several readers would interleave (and repeat) the file order
         self._threads = [threading.Thread(target=self._produce, args=(seed + 1 + i,), daemon=True) for i in range(num_threads)]
         for t in self._threads:
             t.start()

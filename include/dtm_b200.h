@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define DTM_ABI_VERSION 7
+#define DTM_ABI_VERSION 8
 
 /* GEMM epilogues */
 #define DTM_EPI_STORE_F32 0      /* D(fp32)  = alpha * acc          (split-K: red.add into pre-zeroed D) */
@@ -211,6 +211,19 @@ int dtm_tensor_stats_static(const void* x, size_t n, int is_bf16, float* out6, v
 int dtm_histogram(const void* x, size_t n, int is_bf16, const double* limits, int nbins, float* counts, void* stream);
 /* host helper: CRC-32C of a host buffer, continuing from `crc` (TFRecord / checkpoint / event-file codecs). */
 uint32_t dtm_crc32c(const char* data, size_t n, uint32_t crc);
+
+/* ---- native input pipeline (host code; reference: the queue runners of mnist_input.py:44-73) --------------------- */
+/* Reader threads parse TFRecord-framed tf.train.Example records (`image_raw` bytes of exactly image_bytes, `label` int64)
+ * from `files` (shuffled file order, infinite epochs) into a RandomShuffleQueue of capacity min_after_dequeue + 3*batch;
+ * dtm_loader_next blocks until more than min_after_dequeue records are queued, then copies `batch` uniformly drawn records
+ * into pixels_out (uint8 [batch][image_bytes]) and labels_out (int32 [batch]) - typically two regions of one pinned buffer.
+ * shuffle = 0: one reader, file order, FIFO.  A missing file fails dtm_loader_create ("Failed to find file: ..."); corrupt
+ * or mis-sized records fail dtm_loader_next.  Both return their message through dtm_last_error(). */
+void* dtm_loader_create(const char* const* files, int n_files, int batch, int image_bytes, int num_threads, uint64_t seed,
+                        int shuffle, int min_after_dequeue);
+int dtm_loader_next(void* loader, uint8_t* pixels_out, int32_t* labels_out);
+uint64_t dtm_loader_records_read(void* loader);
+void dtm_loader_destroy(void* loader);
 
 /* ---- peer-memory communication (replaces the reference's gRPC parameter-server traffic: main.py:58-60, :80-93;
  *      mnist_input.py:262-267) ------------------------------------------------------------------------------------ */

@@ -364,17 +364,23 @@ def test_convert_mnist_idx_to_png_to_tfrecord_roundtrip(tmp_path):
     assert convert_mnist.main(["convert_mnist.py"]) == 2
 
 
-def test_tfrecord_batches_shuffle_and_validation(tmp_path):
+@pytest.mark.parametrize("native", [False, True])
+def test_tfrecord_batches_shuffle_and_validation(tmp_path, native):
+    """Both implementations of the training input pipeline: Python threads and the C++ loader (record_loader.cpp)."""
     from distributed_tensorflow_ibm_mnist_b200.data import readers
     from distributed_tensorflow_ibm_mnist_b200.formats import tfrecord
+
+    if native and readers._native_loader_lib() is None:
+        pytest.skip("libdtm_b200.so not built")
 
     p = str(tmp_path / "d.tfrecord")
     n = 300
     imgs = [bytes([i % 256]) * 784 for i in range(n)]
     tfrecord.write_mnist_tfrecord(p, imgs, [i % 10 for i in range(n)])
     with pytest.raises(ValueError, match="Failed to find file"):
-        readers.TFRecordBatches([p, str(tmp_path / "missing")], 8, 784)
-    ds = readers.TFRecordBatches([p], 16, 784, min_after_dequeue=50, seed=1)
+        readers.TFRecordBatches([p, str(tmp_path / "missing")], 8, 784, native=native)
+    ds = readers.TFRecordBatches([p], 16, 784, min_after_dequeue=50, seed=1, native=native)
+    assert isinstance(ds, readers.NativeRecordBatches) == native
     assert ds.capacity == 50 + 3 * 16
     x, y = ds.next()
     assert x.shape == (16, 784) and x.dtype == torch.uint8 and y.dtype == torch.int32
@@ -382,10 +388,31 @@ def test_tfrecord_batches_shuffle_and_validation(tmp_path):
     seen = [int(v) for _ in range(10) for v in ds.next()[0][:, 0]]
     assert seen != sorted(seen)                                              # shuffled
     ds.close()
-    bad = readers.TFRecordBatches([p], 4, 2352, min_after_dequeue=0)
+    bad = readers.TFRecordBatches([p], 4, 2352, min_after_dequeue=0, native=native)
     with pytest.raises(ValueError, match="expected 2352"):
         bad.next()
     bad.close()
+    # unshuffled: file order, every record exactly once per epoch
+    seq = readers.TFRecordBatches([p], 50, 784, shuffle=False, native=native)
+    first = [int(v) for _ in range(6) for v in seq.next()[0][:, 0]]
+    assert first == [i % 256 for i in range(300)]
+    seq.close()
+    if native:
+        # a flipped payload byte must be caught by the record CRC, and the packed layout must match the engine's slots
+        raw = bytearray(open(p, "rb").read())
+        raw[40] ^= 0xFF
+        q = str(tmp_path / "corrupt.tfrecord")
+        open(q, "wb").write(bytes(raw))
+        c = readers.TFRecordBatches([q], 4, 784, min_after_dequeue=0, native=True)
+        with pytest.raises(ValueError, match="corrupt TFRecord"):
+            c.next()
+        c.close()
+        ds2 = readers.TFRecordBatches([p], 16, 784, min_after_dequeue=10, seed=3, native=True)
+        buf = ds2.next_packed()
+        assert buf.numel() == ds2.packed_bytes == 16 * 784 + 4 * 16 and ds2.label_offset == 16 * 784
+        lab = buf[ds2.label_offset:].view(torch.int32)
+        assert all(int(buf[i * 784]) % 10 == int(lab[i]) for i in range(16))
+        ds2.close()
     got = list(readers.iter_tfrecord_examples([p]))
     assert len(got) == n and got[3][2] == 3 and got[0][0].endswith(":0")
 
