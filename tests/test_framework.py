@@ -195,6 +195,31 @@ def _torch_engine(preset="reference", B=8, **kw):
     return spec, eng
 
 
+def test_synthetic_batches_are_packed_for_single_copy_staging():
+    """Pixels and labels of a batch share one buffer (pixels | pad to 16 B | int32 labels): the feeder's one-copy path."""
+    from distributed_tensorflow_ibm_mnist_b200.data.synthetic import DeviceFeeder, SyntheticMnist
+
+    for B, px in ((6, 784), (5, 2352), (3, 787)):
+        src = SyntheticMnist(B, px, pool_batches=3, seed=4, pin=False)
+        nb = B * px
+        assert src.label_offset % 16 == 0 and nb <= src.label_offset < nb + 16
+        assert src.packed.shape == (3, src.label_offset + 4 * B)
+        x, y = src.next()
+        buf = src.packed[0]
+        assert x.shape == (B, px) and y.shape == (B,) and y.dtype == torch.int32
+        assert torch.equal(buf[:nb].view(B, px), x) and torch.equal(buf[src.label_offset:].view(torch.int32), y)
+        assert torch.equal(src.next_packed(), src.packed[1])          # the cursor is shared by both accessors
+
+    class _Eng:       # the feeder only takes the packed path when the engine's slot layout matches the source's
+        B, device = 6, torch.device("cpu")
+        packed_label_offset = 6 * 784
+        class spec:
+            image_pixels = 784
+        def stage_packed(self, *a, **k): ...
+    if torch.cuda.is_available():
+        assert DeviceFeeder(_Eng(), SyntheticMnist(6, 784, pool_batches=2, pin=False))._packed
+
+
 def test_torch_engine_learns_separable_data():
     from distributed_tensorflow_ibm_mnist_b200.data.synthetic import SyntheticMnist
 
