@@ -4,11 +4,15 @@ on the device.
 
 Replaces what the reference delegates to TensorFlow's executor inside ``mon_sess.run(train_op)`` (main.py:148-151):
 forward (mnist_input.py:118-208), loss/accuracy (:210-243), autodiff, optimizer apply + EMA + global_step (:246-270).
-Step schedule (``baseline`` preset; ``reference`` adds LRN inside the conv kernels and the local4 GEMMs):
+Step schedule (``baseline`` preset; ``reference`` adds LRN inside the conv kernels, the local4 GEMMs and a separate
+un-pooling kernel).  ``||`` = concurrent branches on forked streams; consecutive kernels are linked by programmatic
+dependent launch edges, so each prologue overlaps its predecessor's tail (DESIGN.md section 2 has the measured timeline):
 
-    conv1_fwd -> conv2_fwd[tcgen05] -> fc GEMM[tcgen05+TMA] -> head_forward(loss)         forward
-    head_backward -> dW3 GEMM || dP2 GEMM -> unpool2 -> conv2_wgrad || conv2_dgrad -> conv1_wgrad   backward
-    fused_update  (or, with >1 rank, the peer-memory all-reduce fused with the same update)       optimizer
+    conv1[tcgen05] -> conv2_fwd[tcgen05] -> fc GEMM[tcgen05+TMA] -> head_forward (loss, dlogits, dH)            forward
+    dP2 GEMM (+ max-pool backward in its epilogue)  ||  head_backward  ||  dW3 GEMM                              fc backward
+    conv2_dgrad -> conv2_wgrad || conv1_wgrad         ||  optimizer update of the fc/head bucket (one CTA per SM)   conv backward
+    optimizer update of the conv bucket + step bookkeeping                                                       close
+  (with > 1 rank both updates are the fused peer-memory exchange: reduce-scatter + optimizer + all-gather in one kernel)
 """
 from __future__ import annotations
 
@@ -55,18 +59,7 @@ class NativeEngine:
         self._side = torch.cuda.Stream(device=self.device)
         self._comm_stream = torch.cuda.Stream(device=self.device)
         self._head_stream = torch.cuda.Stream(device=self.device)
-        self._main_priority = -1 if os.environ.get("DTM_PRIORITY", "0") != "0" else 0
-        # dH inside head_forward pays off while the head's weight rows fit one shared-memory staging chunk (1024 hidden units);
-        # beyond that (the wide preset) the forward kernel would stage every chunk twice
-        self._fuse_dh = (spec.fc2 or spec.fc1) <= 1024
-        # programmatic dependent launch: with the small presets the step is a chain of 10-30 us kernels and hiding the launch
-        # gaps is worth 10 %.  With the wide preset the step is bound by dW3 -> optimizer update on the side streams; early-
-        # resident CTAs of the main-stream chain then take SMs away from exactly those kernels (measured: 536 -> 562 us).
-        self._pdl = 2 if self.flat.total <= (8 << 20) else 0
-        if comm is not None and self.flat.total > (8 << 20) and "DTM_OVERLAP_CTAS" not in os.environ:
-            # wide preset: the fc bucket's exchange runs ~200 us and is bound by the NVSwitch, not by the number of CTAs
-            # (8-GPU sweep: 32 CTAs reach the time of 148) - leave most SMs entirely to the conv backward
-            comm.overlap_ctas = 64
+        self._schedule_policy(comm)
         self._fork_ev = [torch.cuda.Event() for _ in range(10)]
         # gradient buckets in flat-buffer order: the fc/head variables (93 % of the bytes, ready right after the first
         # backward GEMMs) and the conv variables (ready last).  With >1 rank bucket 0 is reduced + updated on its own
@@ -74,20 +67,34 @@ class NativeEngine:
         split = self.flat.offsets["local3/weights"]
         self.buckets = [(split, self.flat.total), (0, split)]
         self.launches_per_step = 0
-        # experiment switches (tools/ablate.py): kernels to leave out of the step (timing only - results are then wrong) and a
-        # flag that puts every kernel on the main stream
-        import os as _os
-        self._skip = set(filter(None, _os.environ.get("DTM_SKIP", "").split(",")))
-        self._serial = _os.environ.get("DTM_SERIAL", "0") == "1"
-        # grid cap of the early optimizer update: one CTA per SM.  conv2_dgrad (capped at 128 registers for this purpose) leaves
-        # room for exactly one update CTA per SM, so the two kernels really run side by side; an uncapped update grid floods
-        # the SMs first and dgrad has to wait for it to drain (measured: 179.6 -> 169.6 us per step)
-        sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
-        # (wide preset: the update itself is the long pole and needs every SM's load slots - no cap)
-        # (reference preset: its LRN backward kernels have a different footprint; the cap measured slower there, 406 -> 429 us)
-        small = self.flat.total <= (8 << 20) and not spec.lrn
-        self._early_update_ctas = int(_os.environ.get("DTM_EARLY_UPDATE_CTAS", str(sm_count if small else 0)))
         self.trace = None   # set to a list to collect (label, cuda event) marks on the main stream (tools/phase_times.py)
+
+    def _schedule_policy(self, comm) -> None:
+        """Measured scheduling choices (tools/ablate.py, tools/timeline.py; numbers in DESIGN.md section 2).  They depend on
+        what bounds the step: a chain of 10-30 us kernels for the small presets, dW3 -> optimizer update for ``wide``."""
+        spec, env = self.spec, os.environ
+        small = self.flat.total <= (8 << 20)
+        self._main_priority = -1 if env.get("DTM_PRIORITY", "0") != "0" else 0     # measured harmful with PDL: off
+        # dH inside head_forward pays off while the head's weight rows fit one shared-memory staging chunk (1024 hidden
+        # units); beyond that (wide) the forward kernel would stage every chunk twice
+        self._fuse_dh = (spec.fc2 or spec.fc1) <= 1024
+        # programmatic dependent launch ("early weights" mode): hiding the launch gaps of the small presets is worth 10 %;
+        # with the wide preset early-resident CTAs of the main chain take SMs away from the kernels that bound the step
+        # (536 -> 562 us), so it is off there
+        self._pdl = 2 if small else 0
+        # grid cap of the early optimizer update: one CTA per SM.  conv2_dgrad is held to 128 registers so that exactly one
+        # update CTA fits beside it on every SM - the two kernels run side by side instead of taking turns (179.6 -> 169.6
+        # us).  No cap for wide (the update is the long pole) nor for the LRN preset (measured slower: 406 -> 429 us).
+        sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
+        self._early_update_ctas = int(env.get("DTM_EARLY_UPDATE_CTAS", str(sm_count if (small and not spec.lrn) else 0)))
+        if comm is not None and not small and "DTM_OVERLAP_CTAS" not in env:
+            # wide: the fc bucket's exchange runs ~200 us and is bound by the NVSwitch, not by the CTA count (8-GPU sweep:
+            # 32 CTAs reach the time of 148) - leave most SMs entirely to the conv backward
+            comm.overlap_ctas = 64
+        # experiment switches (tools/ablate.py): kernels to leave out of the step (timing only - results are then wrong) and
+        # a flag that puts every kernel on the main stream
+        self._skip = set(filter(None, env.get("DTM_SKIP", "").split(",")))
+        self._serial = env.get("DTM_SERIAL", "0") == "1"
 
     # ------------------------------------------------------------------------------------------------
     def _alloc_activations(self, keep_logits: bool) -> None:
