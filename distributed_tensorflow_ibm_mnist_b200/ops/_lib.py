@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_uint32, c_uint64, c_void_p
+from ctypes import c_char_p, c_float, c_int, c_uint32, c_uint64, c_void_p
 from pathlib import Path
 
 ABI_VERSION = 8

@@ -18,7 +18,7 @@ from ctypes import c_int, c_size_t, c_void_p
 import torch
 import torch.distributed as dist
 
-from ..ops import _lib, native
+from ..ops import _lib
 from ..ops._lib import check, current_stream, ptr
 
 MAX_RANKS = 8

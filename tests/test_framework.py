@@ -4,7 +4,6 @@ import json
 import math
 import os
 import struct
-import subprocess
 import sys
 
 import numpy as np

@@ -3,7 +3,6 @@
 Inputs are rounded to bf16 where the kernel consumes bf16, so the comparison isolates the kernel's own arithmetic
 (fp32 accumulation on tensor cores) from input quantisation.
 """
-import math
 
 import pytest
 import torch
