@@ -54,6 +54,10 @@ def test_local_training_checkpoint_resume_and_inference(tmp_path):
     assert "5 steps executed on worker 0." in r.stdout and "[placement]" in r.stdout
     assert os.path.exists(os.path.join(train_dir, "model.ckpt-5.index"))
     assert os.path.exists(os.path.join(train_dir, "model.ckpt-5.data-00000-of-00001"))
+    # the chief's MonitoredTrainingSession artefacts: graph.pbtxt, a MetaGraphDef per checkpoint, an event file in train_dir
+    assert os.path.exists(os.path.join(train_dir, "graph.pbtxt")) and os.path.exists(os.path.join(train_dir, "model.ckpt-5.meta"))
+    assert 'name: "local4/weights/Momentum"' in open(os.path.join(train_dir, "graph.pbtxt")).read()
+    assert len(glob.glob(os.path.join(train_dir, "events.out.tfevents.*"))) == 1
     from distributed_tensorflow_ibm_mnist_b200.formats import checkpoint_state as cs, events
     from distributed_tensorflow_ibm_mnist_b200.formats.tensor_bundle import BundleReader
 
