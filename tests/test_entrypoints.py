@@ -161,3 +161,18 @@ def test_ps_plus_two_workers_gloo_and_validation_inference(tmp_path):
     for row, res in zip(want, doc["results"]):
         assert int(res["label"]) == int(np.argmax(row)) and abs(res["prob"] - row.max()) < 1e-6
     assert doc["accuracy"] == float(np.mean([int(np.argmax(r)) == l for r, l in zip(want, labels)]))
+
+
+def test_tower_mode_spawns_one_worker_per_device(tmp_path):
+    """``--num_gpus=k`` (SURVEY D5 / P-i): one worker process per device on this node, synchronous steps, the chief writes
+    the checkpoints.  On this CPU box the towers fall back to gloo + the portable engine."""
+    train_dir = str(tmp_path / "towers")
+    r = _run(["main.py", "--num_gpus=2", f"--train_dir={train_dir}", "--model=baseline", "--batch_size=8", "--max_steps=6",
+              "--test_interval=3", "--optimizer=momentum", "--base_lr=0.02", "--engine=torch", "--save_checkpoint_secs=-1"])
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert "6 steps executed on worker 0." in r.stdout and "6 steps executed on worker 1." in r.stdout
+    from distributed_tensorflow_ibm_mnist_b200.formats.tensor_bundle import BundleReader
+
+    rd = BundleReader(os.path.join(train_dir, "model.ckpt-6"))
+    assert int(rd.get("global_step")) == 6 and rd.get("conv1/weights").shape == (5, 5, 1, 32)
+    assert os.path.exists(os.path.join(train_dir, "graph.pbtxt"))
