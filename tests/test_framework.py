@@ -194,6 +194,25 @@ def _torch_engine(preset="reference", B=8, **kw):
     return spec, eng
 
 
+def test_philox_mirror_known_answers_and_mask_statistics():
+    """The numpy mirror of the dropout generator (csrc/common/philox.cuh) against the Random123 known-answer vectors of
+    philox4x32-10; the GPU tests then require the kernels' masks to equal this mirror bit for bit."""
+    from distributed_tensorflow_ibm_mnist_b200.ops.philox import dropout_keep_mask, philox4x32_10
+
+    u = lambda v: np.array([v], dtype=np.uint32)
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0), (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for ctr, key, want in kat:
+        got = philox4x32_10(*[u(c) for c in ctr], np.uint32(key[0]), np.uint32(key[1]))
+        assert tuple(int(g[0]) for g in got) == want
+    m1 = dropout_keep_mask(64, 256, seed=7, step=3, keep_prob=0.5)
+    assert m1.shape == (64, 256) and m1.dtype == np.bool_ and 0.45 < m1.mean() < 0.55
+    assert np.array_equal(m1, dropout_keep_mask(64, 256, seed=7, step=3, keep_prob=0.5))          # deterministic
+    assert not np.array_equal(m1, dropout_keep_mask(64, 256, seed=7, step=4, keep_prob=0.5))      # step dependent
+    assert dropout_keep_mask(8, 64, seed=1, step=0, keep_prob=0.9).mean() > 0.8
+
+
 def test_synthetic_batches_are_packed_for_single_copy_staging():
     """Pixels and labels of a batch share one buffer (pixels | pad to 16 B | int32 labels): the feeder's one-copy path."""
     from distributed_tensorflow_ibm_mnist_b200.data.synthetic import DeviceFeeder, SyntheticMnist
