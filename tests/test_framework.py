@@ -380,6 +380,29 @@ def test_graph_pbtxt_and_step_counter(tmp_path):
     assert not any(step == 12 for step, _ in tags) and hook.last_rate > 0
 
 
+def test_collective_saves_over_gloo(tmp_path):
+    """Sharded engines need every rank inside ``save`` (the optimizer state is gathered from its owners): the chief's
+    time-based decision is broadcast at fixed step intervals and all ranks act on it together; only the chief writes."""
+    import json
+    import socket
+    import subprocess
+    import sys
+
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    worker = os.path.join(os.path.dirname(__file__), "helpers", "collective_save_worker.py")
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", OMP_NUM_THREADS="2")
+    procs = [subprocess.Popen([sys.executable, worker, str(r), "2", str(port), str(tmp_path)], env=env,
+                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(2)]
+    outs = [p.communicate(timeout=240) for p in procs]
+    assert all(p.returncode == 0 for p in procs), [o[1][-1500:] for o in outs]
+    c0 = json.load(open(tmp_path / "calls0.json"))["calls"]
+    c1 = json.load(open(tmp_path / "calls1.json"))["calls"]
+    assert [c[0] for c in c0] == [c[0] for c in c1] == [4, 8, 10]          # two polled saves + the final one, in lock step
+    assert all(w for _, w in c0) and not any(w for _, w in c1)              # only the chief writes
+    files = sorted(os.listdir(tmp_path / "train"))
+    assert "model.ckpt-10.index" in files and "model.ckpt-4.index" in files and "checkpoint" in files
+
+
 def test_convert_mnist_idx_to_png_to_tfrecord_roundtrip(tmp_path):
     sys.path.insert(0, ROOT)
     import convert_mnist
