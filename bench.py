@@ -100,6 +100,8 @@ class ClockSampler:
 
 
 def reference_arm() -> None:
+    if int(os.environ.get("RANK", "0")) != 0:     # launched with torchrun for N > 1: ONE line, from rank 0
+        return
     print(json.dumps({
         "impl": "reference",
         "unavailable": "reference is 5 loose TF-1.x/py2 scripts: pip reports 'neither setup.py nor pyproject.toml', "
