@@ -99,19 +99,32 @@ def png2tfrecord(png_root, out_file, channels=1, shuffle=False, seed=0):
 
 
 def main(argv):
-    args = [a for a in argv[1:] if not a.startswith("--")]
-    opts = [a for a in argv[1:] if a.startswith("--")]
-    channels, shuffle, quiet = 1, False, False
-    for o in opts:
-        if o.startswith("--channels"):
-            channels = int(o.split("=", 1)[1]) if "=" in o else 3
-        elif o == "--shuffle":
+    args, channels, shuffle, quiet = [], 1, False, False
+    it = iter(argv[1:])
+    for a in it:
+        if a.startswith("--channels"):      # --channels=3, --channels 3, or bare --channels (= 3)
+            if "=" in a:
+                channels = int(a.split("=", 1)[1])
+            else:
+                nxt = next(it, None)
+                if nxt is not None and nxt.isdigit():
+                    channels = int(nxt)
+                else:
+                    channels = 3
+                    if nxt is not None:
+                        args.append(nxt)
+        elif a == "--shuffle":
             shuffle = True
-        elif o == "--quiet":
+        elif a == "--quiet":
             quiet = True
-        else:
-            print(f"unknown option {o}", file=sys.stderr)
+        elif a.startswith("--"):
+            print(f"unknown option {a}", file=sys.stderr)
             return 2
+        else:
+            args.append(a)
+    if channels not in (1, 3):
+        print("--channels must be 1 or 3", file=sys.stderr)
+        return 2
     if len(args) == 3 and args[0] == "idx2png":
         idx2png(args[1], args[2], verbose=not quiet)
     elif len(args) == 3 and args[0] == "png2tfrecord":

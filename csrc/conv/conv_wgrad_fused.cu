@@ -1,0 +1,315 @@
+// Both convolution weight gradients of the MNIST CNN in ONE tcgen05 kernel (autodiff of mnist_input.py:142-147 and :161):
+//
+//   dW2[kh][kw][ci][co] = sum_{image, pixel} P1[pixel + tap][ci] * dZ2[pixel][co]          (conv2, exactly conv2_wgrad.cu)
+//   dW1[kh][kw][0][co]  = sum_{image, pixel} X[pixel + tap]      * dZ1[pixel][co]          (conv1, C_in = 1)
+//   db1[co]             = sum_{image, pixel} dZ1[pixel][co]
+//
+// Why one kernel: in round 1 the conv1 gradient ran as a CUDA-core kernel beside conv2_wgrad (one LDS + one FFMA per
+// multiply-add, 11.8 M instructions; 29 us alone, 43 us while sharing the SMs) and ended the backward pass 13 us after
+// conv2_wgrad.  conv2_wgrad leaves six of its eight warps idle until the epilogue and 96 of its 512 TMEM columns unused -
+// here those warps build the conv1 operands in shared memory and the MMA warp issues 56 more tcgen05.mma per conv1 image
+// into a spare accumulator.
+//
+// conv1 on the tensor core without im2col ("shifted window" operand).  K = pixels, like conv2.  The un-pooled gradient dZ1
+// is stored per image as 4 planes [28 rows x 32 pixels][8 channels] (pixels 16 B apart: the same MN-major core matrices as
+// the conv2 planes).  The image side is ONE 16-byte entry per pixel, E[p][s] = Xp[p + s], s = 0..7 (Xp = normalised image with
+// a 2-pixel zero halo, row pitch 32): read as an MN-major operand whose M index is m = kh * 8 + kw, the 8 kw of a group
+// are the 8 bf16 of an entry, the kh groups are one image row (512 B) apart, and K advances 16 B per pixel:
+//     A[k = p][m = (kh, kw)] = E[p + 32 kh][kw] = Xp[h + kh][w + kw]
+// which is exactly the pixel that filter tap (kh, kw) pairs with output pixel p = (h, w) under SAME padding.  M = 64 holds
+// kh = 0..7 x kw = 0..7; rows with kh > 4 or kw > 4 are computed from whatever follows in shared memory and never stored -
+// except m = 5, whose entries' slot 5 is set to 1.0, so that D[5][co] is the bias gradient.  Producer cost per image:
+// 896 16-byte stores for the image side (an explicit im2col needs 4x that and a gather per element) + the un-pooling.
+//
+// Work split: blockIdx.y halves the conv2 taps (13 | 12) as before; both halves walk the same images, and the conv1 part
+// of image iteration `it` is done by the half with the lighter tap group on even, the heavier on odd iterations.
+#include "../common/ptx.cuh"
+#include "../common/host_util.h"
+#include "../../include/dtm_b200.h"
+#include "plane_layout.cuh"
+
+namespace dtm {
+
+constexpr int FW_CI = 32, FW_CO = 64, FW_C1 = 32;
+constexpr int FW_P1_BYTES = plane_image_bytes(FW_CI);    // 16384
+constexpr int FW_DZ_BYTES = plane_image_bytes(FW_CO);    // 32768
+constexpr int FW_STAGE_BYTES = PL_GUARD_BYTES + FW_P1_BYTES + PL_GUARD_BYTES + FW_DZ_BYTES;  // 53248
+constexpr int FW_STAGES = 2;
+constexpr int FW_TAPS_Y0 = 13;
+// conv1 operands
+constexpr int FW_PITCH = 32;                               // pixels per stored image row (28 + halo / padding)
+constexpr int FW_ROWS = 28;                                // output rows = K rows
+constexpr int FW_E_ROWS = 35;                              // entry rows reachable by kh = 0..7 from output rows 0..27
+constexpr int FW_E_BYTES = FW_E_ROWS * FW_PITCH * 16;      // 17920
+constexpr int FW_Z1_PLANE = FW_ROWS * FW_PITCH * 16;       // 14336
+constexpr int FW_Z1_BYTES = (FW_C1 / 8) * FW_Z1_PLANE;     // 57344
+constexpr int FW_XP_PITCH = 40;                            // bf16 halo image: 32 rows x 40 columns (column w + 7 <= 38)
+constexpr int FW_XP_BYTES = 32 * FW_XP_PITCH * 2;          // 2560
+constexpr int FW_SMEM = FW_STAGES * FW_STAGE_BYTES + FW_E_BYTES + FW_Z1_BYTES + FW_XP_BYTES + 128;
+constexpr int FW_BUILDERS = 192;                           // warps 2..7
+constexpr int FW_C1_STEPS = FW_ROWS * FW_PITCH / 16;       // 56 MMAs per conv1 image
+
+// conv2 MMAs of one image for this CTA's tap group (same schedule as conv2_wgrad.cu)
+template <bool FIRST_IMAGE>
+DTM_DEVICE void fw_issue_conv2(uint32_t tmem_base, const UmmaDescBase& dz_base, const UmmaDescBase& p1_base, int tap0, int ntaps,
+                               uint32_t idesc) {
+#pragma unroll 1
+  for (int ks = PL_ROW_OFF; ks < PL_GRID; ++ks) {
+    const uint64_t da = umma_desc_at(dz_base, ks * 256);
+    const bool first = FIRST_IMAGE && ks == PL_ROW_OFF;
+#pragma unroll
+    for (int tl = 0; tl < FW_TAPS_Y0; ++tl) {
+      if (tl < ntaps) {
+        const int tap_a = tl, tap_b = FW_TAPS_Y0 + tl;
+        const int off_a = (((tap_a / 5) - 2) * PL_GRID + (tap_a % 5) - 2) * 16;
+        const int off_b = (((tap_b / 5) - 2) * PL_GRID + (tap_b % 5) - 2) * 16;
+        const uint64_t db = umma_desc_at(p1_base, ks * 256 + (tap0 == 0 ? off_a : off_b));
+        if (first) umma_f16_c<false>(tmem_base + tl * FW_CI, da, db, idesc);
+        else       umma_f16_c<true>(tmem_base + tl * FW_CI, da, db, idesc);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256, 1)
+conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __restrict__ dz2_planes,
+                        const uint8_t* __restrict__ x_u8, const __nv_bfloat16* __restrict__ grad_pooled,
+                        const uint8_t* __restrict__ argmax, int batch, float* __restrict__ dw2, float* __restrict__ dw1,
+                        float* __restrict__ db1) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[FW_STAGES], empty_bar[FW_STAGES], done_bar, c1_full, c1_empty;
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  uint8_t* s_e = smem + FW_STAGES * FW_STAGE_BYTES;       // image entries E[row][pixel][8 shifts]
+  uint8_t* s_z1 = s_e + FW_E_BYTES;                       // un-pooled conv1 gradient, 4 planes
+  __nv_bfloat16* s_xp = reinterpret_cast<__nv_bfloat16*>(s_z1 + FW_Z1_BYTES);   // halo image, bf16
+
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t lane = lane_id();
+  const int y = blockIdx.y;
+  const int tap0 = y == 0 ? 0 : FW_TAPS_Y0;
+  const int ntaps = y == 0 ? FW_TAPS_Y0 : 25 - FW_TAPS_Y0;
+  const int first = blockIdx.x, stride = gridDim.x;
+  const int n_it = (batch - first + stride - 1) / stride;
+  // conv1 images of this CTA: iterations with (it & 1) != y  (y = 1, the 12-tap group, takes the even ones)
+  const int n_c1 = y == 1 ? (n_it + 1) / 2 : n_it / 2;
+
+  if (warp == 1 && elect_one()) {
+    for (int i = 0; i < FW_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(&done_bar, 1);
+    mbar_init(&c1_full, FW_BUILDERS);
+    mbar_init(&c1_empty, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) { tmem_alloc(&tmem_slot, 512); tmem_relinquish(); }
+  {
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    // guards around every P1 buffer (taps over-read into them; they must hold finite zeros)
+    for (int s = 0; s < FW_STAGES; ++s) {
+      uint8_t* st = smem + s * FW_STAGE_BYTES;
+      for (int i = threadIdx.x * 16; i < PL_GUARD_BYTES; i += blockDim.x * 16) {
+        *reinterpret_cast<uint4*>(st + i) = z;
+        *reinterpret_cast<uint4*>(st + PL_GUARD_BYTES + FW_P1_BYTES + i) = z;
+      }
+    }
+    // conv1 side: gradient planes (their padding pixels stay zero for good), halo image, and the entry rows that never
+    // change - rows 0,1 and 30..34 pair with halo rows (zero image) and only carry the bias-gradient 1.0 in slot 5
+    for (int i = threadIdx.x * 16; i < FW_Z1_BYTES + FW_XP_BYTES; i += blockDim.x * 16) *reinterpret_cast<uint4*>(s_z1 + i) = z;
+    const uint4 ones = make_uint4(0, 0, 0x3F800000u, 0);       // slot 5 = bf16 1.0
+    for (int i = threadIdx.x; i < FW_E_ROWS * FW_PITCH; i += blockDim.x) {
+      const int rr = i / FW_PITCH;
+      if (rr < 2 || rr >= 30) *reinterpret_cast<uint4*>(s_e + i * 16) = ones;
+    }
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  pdl_wait();                 // every operand comes from preceding kernels
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    // ------------------------------ bulk-copy producer (conv2 operands) ------------------------------
+    if (elect_one()) {
+      int it = 0;
+      for (int img = first; img < batch; img += stride, ++it) {
+        const int s = it % FW_STAGES;
+        mbar_wait(&empty_bar[s], ((it / FW_STAGES) & 1) ^ 1, 30);
+        mbar_arrive_expect_tx(&full_bar[s], FW_P1_BYTES + FW_DZ_BYTES);
+        uint8_t* st = smem + s * FW_STAGE_BYTES;
+        bulk_load_1d(st + PL_GUARD_BYTES, p1_planes + static_cast<size_t>(img) * FW_P1_BYTES, FW_P1_BYTES, &full_bar[s]);
+        bulk_load_1d(st + 2 * PL_GUARD_BYTES + FW_P1_BYTES, dz2_planes + static_cast<size_t>(img) * FW_DZ_BYTES, FW_DZ_BYTES,
+                     &full_bar[s]);
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer ------------------------------
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(64, FW_CI, true, true);
+      const UmmaDescBase e_base = umma_desc_base(smem_u32(s_e), 128, FW_PITCH * 16, UMMA_SWIZZLE_NONE);
+      const UmmaDescBase z1_base = umma_desc_base(smem_u32(s_z1), 128, FW_Z1_PLANE, UMMA_SWIZZLE_NONE);
+      const uint32_t tmem_c1 = tmem_base + ntaps * FW_CI;
+      int it = 0, j = 0;
+      for (int img = first; img < batch; img += stride, ++it) {
+        const int s = it % FW_STAGES;
+        mbar_wait(&full_bar[s], (it / FW_STAGES) & 1, 31);
+        tc_fence_after();
+        const UmmaDescBase p1_base = umma_desc_base(smem_u32(smem + s * FW_STAGE_BYTES + PL_GUARD_BYTES), 128, PL_PLANE_BYTES, UMMA_SWIZZLE_NONE);
+        const UmmaDescBase dz_base = umma_desc_base(smem_u32(smem + s * FW_STAGE_BYTES + 2 * PL_GUARD_BYTES + FW_P1_BYTES), 128,
+                                                    PL_PLANE_BYTES, UMMA_SWIZZLE_NONE);
+        if (it == 0) fw_issue_conv2<true>(tmem_base, dz_base, p1_base, tap0, ntaps, idesc);
+        else         fw_issue_conv2<false>(tmem_base, dz_base, p1_base, tap0, ntaps, idesc);
+        umma_commit(&empty_bar[s]);
+        if ((it & 1) != y) {
+          mbar_wait(&c1_full, j & 1, 33);
+          tc_fence_after();
+          if (j == 0) umma_f16_c<false>(tmem_c1, umma_desc_at(e_base, 0), umma_desc_at(z1_base, 0), idesc);
+          else        umma_f16_c<true>(tmem_c1, umma_desc_at(e_base, 0), umma_desc_at(z1_base, 0), idesc);
+#pragma unroll 5
+          for (int i = 1; i < FW_C1_STEPS; ++i)
+            umma_f16_c<true>(tmem_c1, umma_desc_at(e_base, i * 256), umma_desc_at(z1_base, i * 256), idesc);
+          umma_commit(&c1_empty);
+          ++j;
+        }
+      }
+      umma_commit(&done_bar);
+    }
+  } else {
+    // ------------------------------ conv1 operand builders (warps 2..7) ------------------------------
+    const int bt = threadIdx.x - 64;        // 0..191
+    int it = 0, j = 0;
+    for (int img = first; img < batch; img += stride, ++it) {
+      if ((it & 1) == y) continue;
+      // global loads of this image first: they are in flight while the previous conv1 image's MMAs are awaited
+      const uint8_t* xs = x_u8 + static_cast<size_t>(img) * 784;
+      uint32_t xw[2] = {0, 0};
+      if (bt < 196) xw[0] = *reinterpret_cast<const uint32_t*>(xs + bt * 4);     // 196 words = 784 bytes (bt < 192 here)
+      if (bt < 4) xw[1] = *reinterpret_cast<const uint32_t*>(xs + (192 + bt) * 4);
+      const __nv_bfloat16* gs = grad_pooled + static_cast<size_t>(img) * (IMG * IMG) * FW_C1;
+      const uint8_t* as = argmax + static_cast<size_t>(img) * (IMG * IMG) * FW_C1;
+      uint4 gv[5];
+      uint2 av[5];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const int item = bt + k * FW_BUILDERS;          // item = cg * 196 + pp
+        if (item < 4 * IMG * IMG) {
+          const int cg = item / (IMG * IMG), pp = item - cg * (IMG * IMG);
+          gv[k] = *reinterpret_cast<const uint4*>(gs + pp * FW_C1 + cg * 8);
+          av[k] = *reinterpret_cast<const uint2*>(as + pp * FW_C1 + cg * 8);
+        }
+      }
+      mbar_wait(&c1_empty, (j & 1) ^ 1, 34);
+      // 1. halo image in bf16: Xp[r + 2][c + 2] = x[r][c] / 255 - 0.5
+      {
+        auto put4 = [&](int word, uint32_t v) {
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            const int px = word * 4 + b, r = px / 28, c = px - r * 28;
+            s_xp[(r + 2) * FW_XP_PITCH + c + 2] = __float2bfloat16(static_cast<float>((v >> (8 * b)) & 0xFF) * (1.0f / 255.0f) - 0.5f);
+          }
+        };
+        put4(bt, xw[0]);
+        if (bt < 4) put4(192 + bt, xw[1]);
+      }
+      asm volatile("bar.sync 1, 192;" ::: "memory");
+      // 2. entries of rows 2..29: E[rr][w][s] = Xp[rr][w + s], slot 5 := 1.0
+      for (int e = bt; e < 28 * FW_PITCH; e += FW_BUILDERS) {
+        const int rr = 2 + e / FW_PITCH, w = e % FW_PITCH;
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(s_xp + rr * FW_XP_PITCH) + (w >> 1);
+        uint32_t r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3];
+        if (w & 1) {
+          const uint32_t r4 = row[4];
+          r0 = __funnelshift_r(r0, r1, 16); r1 = __funnelshift_r(r1, r2, 16);
+          r2 = __funnelshift_r(r2, r3, 16); r3 = __funnelshift_r(r3, r4, 16);
+        }
+        r2 = (r2 & 0x0000FFFFu) | 0x3F800000u;
+        *reinterpret_cast<uint4*>(s_e + (rr * FW_PITCH + w) * 16) = make_uint4(r0, r1, r2, r3);
+      }
+      // 3. un-pooled gradient: pooled pixel (ph, pw), channel group cg -> its four window positions
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const int item = bt + k * FW_BUILDERS;
+        if (item < 4 * IMG * IMG) {
+          const int cg = item / (IMG * IMG), pp = item - cg * (IMG * IMG);
+          const int ph = pp / IMG, pw = pp - ph * IMG;
+          const uint32_t gw[4] = {gv[k].x, gv[k].y, gv[k].z, gv[k].w};
+          uint8_t* dst = s_z1 + cg * FW_Z1_PLANE + ((2 * ph) * FW_PITCH + 2 * pw) * 16;
+#pragma unroll
+          for (int d = 0; d < 4; ++d) {
+            uint32_t z[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const uint32_t a0 = ((t < 2 ? av[k].x : av[k].y) >> (16 * (t & 1))) & 0xFF;
+              const uint32_t a1 = ((t < 2 ? av[k].x : av[k].y) >> (16 * (t & 1) + 8)) & 0xFF;
+              z[t] = (a0 == static_cast<uint32_t>(d) ? (gw[t] & 0x0000FFFFu) : 0u) | (a1 == static_cast<uint32_t>(d) ? (gw[t] & 0xFFFF0000u) : 0u);
+            }
+            *reinterpret_cast<uint4*>(dst + ((d >> 1) * FW_PITCH + (d & 1)) * 16) = make_uint4(z[0], z[1], z[2], z[3]);
+          }
+        }
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&c1_full);
+      asm volatile("bar.sync 1, 192;" ::: "memory");     // nobody still reads the halo image when the next one is staged
+      ++j;
+    }
+    if (warp >= 4) {
+      // ------------------------------ epilogue ------------------------------
+      const uint32_t q = warp & 3;
+      mbar_wait(&done_bar, 0, 32);
+      tc_fence_after();
+      const int row = q * 16 + lane;  // accumulator row (M = 64: lanes 0-15 of each quadrant), valid for lane < 16
+#pragma unroll 1
+      for (int tl = 0; tl < ntaps; ++tl) {
+        uint32_t r[32];
+        tmem_ld_x32(tmem_base + ((q * 32u) << 16) + tl * FW_CI, r);
+        tmem_ld_wait();
+        if (lane < 16) {
+          float* dst = dw2 + static_cast<size_t>(tap0 + tl) * FW_CI * FW_CO + row;
+#pragma unroll
+          for (int ci = 0; ci < FW_CI; ++ci) red_add_f32(dst + ci * FW_CO, __uint_as_float(r[ci]));
+        }
+      }
+      if (n_c1 > 0) {
+        uint32_t r[32];
+        tmem_ld_x32(tmem_base + ((q * 32u) << 16) + ntaps * FW_CI, r);
+        tmem_ld_wait();
+        const int kh = row >> 3, kw = row & 7;
+        if (lane < 16 && kh < 5 && kw < 5) {
+          float* dst = dw1 + (kh * 5 + kw) * FW_C1;
+#pragma unroll
+          for (int c = 0; c < FW_C1; ++c) red_add_f32(dst + c, __uint_as_float(r[c]));
+        } else if (lane < 16 && row == 5) {
+#pragma unroll
+          for (int c = 0; c < FW_C1; ++c) red_add_f32(db1 + c, __uint_as_float(r[c]));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace dtm
+
+extern "C" int dtm_conv_wgrad_fused(const void* p1_planes, const void* dz2_planes, const void* x_u8, const void* grad_pooled,
+                                    const void* argmax, int batch, float* dw2, float* dw1, float* db1, void* stream) {
+  using namespace dtm;
+  if (batch <= 0) return dtm_fail("conv_wgrad_fused: batch must be positive");
+  if (!p1_planes || !dz2_planes || !x_u8 || !grad_pooled || !argmax || !dw2 || !dw1 || !db1)
+    return dtm_fail("conv_wgrad_fused: null argument");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  static bool configured = false;
+  if (!configured) {
+    DTM_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FW_SMEM));
+    configured = true;
+  }
+  const int gx = min(batch, max(1, device_sm_count() / 2));
+  DTM_CUDA_OK(launch_pdl(conv_wgrad_fused_kernel, dim3(gx, 2), dim3(256), FW_SMEM, s, static_cast<const uint8_t*>(p1_planes),
+                         static_cast<const uint8_t*>(dz2_planes), static_cast<const uint8_t*>(x_u8),
+                         static_cast<const __nv_bfloat16*>(grad_pooled), static_cast<const uint8_t*>(argmax), batch, dw2, dw1, db1));
+  DTM_CUDA_OK(cudaGetLastError());
+  return 0;
+}

@@ -59,6 +59,23 @@ def _q(x: torch.Tensor, on: bool) -> torch.Tensor:
     return x.to(torch.bfloat16).to(torch.float32) if on else x
 
 
+class _RoundGradToBf16(torch.autograd.Function):
+    """Identity whose backward rounds the incoming gradient to bf16 - placed where the sm_100a backward pass stores a
+    gradient tensor as bf16 (dH, dP2 / dZ2, dPool1), so that the oracle's gradients carry the same quantisation."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).to(g.dtype)
+
+
+def _qg(x: torch.Tensor, on: bool) -> torch.Tensor:
+    return _RoundGradToBf16.apply(x) if (on and x.requires_grad) else x
+
+
 def normalise_u8(images_u8: torch.Tensor) -> torch.Tensor:
     """``tf.cast(image, tf.float32) * (1. / 255) - 0.5`` — mnist_input.py:39."""
     return images_u8.to(torch.float32) * (1.0 / 255.0) - 0.5
@@ -77,22 +94,22 @@ def forward(params: dict[str, torch.Tensor], images: torch.Tensor, spec: ModelSp
     w1 = _q(params["conv1/weights"], q).permute(3, 2, 0, 1)
     a1 = F.relu(F.conv2d(x, w1, params["conv1/biases"], padding=2))
     acts["conv1"] = a1
-    p1 = F.max_pool2d(a1, 2)
+    p1 = _qg(F.max_pool2d(a1, 2), q)          # conv2_dgrad stores the gradient of the pooled activation as bf16
     if spec.lrn:
         p1 = tf_lrn(_q(p1, q))
     p1 = _q(p1, q)
     w2 = _q(params["conv2/weights"], q).permute(3, 2, 0, 1)
-    a2 = F.relu(F.conv2d(p1, w2, params["conv2/biases"], padding=2))
+    a2 = F.relu(_qg(F.conv2d(p1, w2, params["conv2/biases"], padding=2), q))   # dZ2 planes are bf16
     acts["conv2"] = a2
     if spec.lrn:
         a2 = tf_lrn(_q(a2, q))
-    p2 = _q(F.max_pool2d(a2, 2), q)
+    p2 = _qg(_q(F.max_pool2d(a2, 2), q), q)   # dP2 is bf16
     flat = p2.permute(0, 2, 3, 1).reshape(B, -1)
-    h = F.relu(flat @ _q(params["local3/weights"], q) + params["local3/biases"])
+    h = F.relu(_qg(flat @ _q(params["local3/weights"], q) + params["local3/biases"], q))   # dH of local3 is bf16
     acts["local3"] = h
     if spec.fc2:
         h = _q(h, q)
-        h = F.relu(h @ _q(params["local4/weights"], q) + params["local4/biases"])
+        h = F.relu(_qg(h @ _q(params["local4/weights"], q) + params["local4/biases"], q))
         acts["local4"] = h
     if dropout_mask is not None and spec.keep_prob < 1.0:
         h = h * dropout_mask.to(h.dtype) / spec.keep_prob

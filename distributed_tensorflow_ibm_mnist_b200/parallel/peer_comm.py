@@ -289,12 +289,15 @@ class PeerComm:
     def barrier(self) -> None:
         dist.barrier(group=self.group)
 
-    def close(self) -> None:
+    def close(self, collective: bool = True) -> None:
+        """Unmap and free the symmetric buffers.  ``collective=False`` skips the rendezvous with the other ranks (error paths:
+        a rank that is going down must not wait for peers that may already be gone)."""
         torch.cuda.synchronize(self.device)
-        try:
-            dist.barrier(group=self.group)
-        except Exception:
-            pass
+        if collective:
+            try:
+                dist.barrier(group=self.group)
+            except Exception:
+                pass
         for b in self._buffers:
             b.close()
         self._buffers = []

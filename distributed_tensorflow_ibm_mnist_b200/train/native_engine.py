@@ -91,6 +91,10 @@ class NativeEngine:
             # wide: the fc bucket's exchange runs ~200 us and is bound by the NVSwitch, not by the CTA count (8-GPU sweep:
             # 32 CTAs reach the time of 148) - leave most SMs entirely to the conv backward
             comm.overlap_ctas = 64
+        # one tcgen05 kernel for both convolution weight gradients (conv1's operands are built by the warps that idle in
+        # conv2_wgrad): single-channel uint8 input only.  Opt-in (DTM_WGRAD_FUSED=1) until it beats the two separate
+        # kernels inside the step (first measurement: 171 vs 161 us per step)
+        self._fused_wgrad = spec.channels == 1 and env.get("DTM_WGRAD_FUSED", "0") == "1"
         # experiment switches (tools/ablate.py): kernels to leave out of the step (timing only - results are then wrong) and
         # a flag that puts every kernel on the main stream
         self._skip = set(filter(None, env.get("DTM_SKIP", "").split(",")))
@@ -333,20 +337,26 @@ class NativeEngine:
             native.conv2_dgrad(self.dz2, f.weight_bf16("conv2/weights"), self.p1, self.pool_raw, self.dpool1, batch=B, lrn=s.lrn,
                                packed=self.w2_dgrad); n += 1
         self._mark("conv2_dgrad")
-        # conv2_wgrad is the longer of the two weight-gradient kernels: it stays on the main stream (programmatic edge from
-        # dgrad, no cross-stream hand-off on the critical path); conv1_wgrad (26 KB of smem, CUDA cores) co-resides with it
-        self._fork_ev[2].record(main)
-        self._side.wait_event(self._fork_ev[2])
-        with torch.cuda.stream(self._stream(self._side)):
-            if self._on("conv1_wgrad"):
-                native.conv1_wgrad(x, self.dpool1, self.arg1, f.gradient("conv1/weights"), f.gradient("conv1/biases"),
-                                   channels=s.channels); n += 1
-            self._fork_ev[3].record(self._side)
-        if self._on("conv2_wgrad"):
-            native.conv2_wgrad(self.p1, self.dz2, f.gradient("conv2/weights"), batch=B); n += 1
+        fused_wgrad = self._fused_wgrad and x.dtype == torch.uint8 and self._on("conv2_wgrad") and self._on("conv1_wgrad")
+        if fused_wgrad:
+            native.conv_wgrad_fused(self.p1, self.dz2, x, self.dpool1, self.arg1, f.gradient("conv2/weights"),
+                                    f.gradient("conv1/weights"), f.gradient("conv1/biases"), batch=B); n += 1
+        else:
+            # conv2_wgrad is the longer of the two weight-gradient kernels: it stays on the main stream (programmatic edge
+            # from dgrad, no cross-stream hand-off on the critical path); conv1_wgrad (26 KB of smem, CUDA cores) co-resides
+            self._fork_ev[2].record(main)
+            self._side.wait_event(self._fork_ev[2])
+            with torch.cuda.stream(self._stream(self._side)):
+                if self._on("conv1_wgrad"):
+                    native.conv1_wgrad(x, self.dpool1, self.arg1, f.gradient("conv1/weights"), f.gradient("conv1/biases"),
+                                       channels=s.channels); n += 1
+                self._fork_ev[3].record(self._side)
+            if self._on("conv2_wgrad"):
+                native.conv2_wgrad(self.p1, self.dz2, f.gradient("conv2/weights"), batch=B); n += 1
         self._mark("conv1_wgrad")
         main.wait_event(self._fork_ev[1])
-        main.wait_event(self._fork_ev[3])
+        if not fused_wgrad:
+            main.wait_event(self._fork_ev[3])
         if self._on("head_bwd") and self._fuse_dh:
             main.wait_event(self._fork_ev[7])
         if fused_unpool:
@@ -435,12 +445,23 @@ class NativeEngine:
         self._forward(self.x[slot], self.y[slot], training=True, state=self.eval_state, count=count)
         self._backward(self.x[slot], count, with_comm=False)
 
+    def weight_loss(self) -> float:
+        """Sum of the ``wd * l2_loss(w)`` terms of the 'losses' collection (mnist_input.py:113) for the current weights.  A
+        sharded engine reads the bf16 shadow of the fc matrices (their fp32 masters live on the owning rank only)."""
+        total = 0.0
+        for v in self.spec.variables:
+            if v.wd:
+                w = self.flat.weight_bf16(v.name).float() if (self.sharded and v.tensor_core_only) else self.flat.weight(v.name)
+                total += 0.5 * float(v.wd) * float((w * w).sum())
+        return total
+
     def evaluate(self, slot: int = 0) -> tuple[float, float]:
-        """Loss and accuracy of the staged batch without touching weights (the reference's "test" summaries)."""
+        """(total loss, accuracy) of the staged batch without touching weights - the reference's "test" summaries, which
+        fetch the same ``total_loss`` tensor as the train summaries (main.py:103-106): cross-entropy + weight-decay terms."""
         native.state_init(self.eval_state)
         self._forward(self.x[slot], self.y[slot], training=False, state=self.eval_state)
         st = native.read_state(self.eval_state)
-        return st.loss_sum, st.correct
+        return st.loss_sum + self.weight_loss(), st.correct
 
     def predict(self, images: torch.Tensor) -> torch.Tensor:
         """Class probabilities for ``images`` ([n <= B, pixels], uint8 raw or float32 already normalised)."""
@@ -468,8 +489,15 @@ class NativeEngine:
 
     def summary_tensors(self) -> dict:
         """Tensors for the chief's summaries (main.py:95-109).  Gradients are recomputed on the last batch with an extra
-        forward/backward pass: the fused update kernel clears accumulated gradients as it consumes them."""
+        forward/backward pass: the fused update kernel clears accumulated gradients as it consumes them.
+
+        Multi-GPU: only the chief calls this, while its peers have already launched their next step.  That is safe for one
+        reason only: a peer's next exchange kernel waits in its first cross-GPU barrier until the chief launches the matching
+        kernel, and no peer reads the chief's gradient buffer before that barrier - so the buffer is private to this rank for
+        the duration of this call.  The device must therefore be idle on entry (nothing of the previous step may still be
+        reducing out of ``flat.grad``): the synchronize below enforces it instead of relying on the caller."""
         slot = getattr(self, "_last_slot", 0)
+        torch.cuda.synchronize(self.device)
         self.flat.grad.zero_()
         self.forward_backward(slot)
         grads = {v.name: self.flat.gradient(v.name).clone() for v in self.spec.variables}

@@ -123,9 +123,12 @@ class TorchEngine:
         self._last_wl = wl
 
     def evaluate(self, slot: int = 0) -> tuple[float, float]:
+        """(total loss, accuracy) of the staged batch.  The reference feeds ONE tensor - ``total_loss``, cross-entropy plus
+        the weight-decay terms - to both the 'train loss' and the 'test loss' scalar (main.py:103-106), so the test value
+        includes the l2 terms as well; otherwise the two TensorBoard curves are not comparable."""
         with torch.no_grad():
             logits, _, total, xent = self._forward_loss(slot, training=False)
-            return float(xent), float(oracle.accuracy_fn(logits, self.y[slot]))
+            return float(total), float(oracle.accuracy_fn(logits, self.y[slot]))
 
     def predict(self, images: torch.Tensor) -> torch.Tensor:
         with torch.no_grad():

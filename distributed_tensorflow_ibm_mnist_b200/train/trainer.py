@@ -60,7 +60,10 @@ class NanLossHook(Hook):
     def _check(self, loop) -> None:
         m = loop.engine.metrics()
         loss = m.get("total_loss", m.get("cross_entropy", 0.0))
-        if m.get("nan") or (isinstance(loss, float) and (math.isnan(loss) or math.isinf(loss))):
+        bad = bool(m.get("nan")) or (isinstance(loss, float) and (math.isnan(loss) or math.isinf(loss)))
+        # synchronous replicas take this decision together: a rank that stopped alone would leave its peers waiting in the
+        # next step's cross-GPU barrier until the watchdog kills them (every rank polls on the same local step)
+        if loop.any_rank(bad):
             if self.fail:
                 raise NanLossError(f"NaN loss during training at global step {m.get('global_step')}")
             loop.ctx.request_stop()
@@ -195,6 +198,19 @@ class MonitoredTrainingLoop:
             self.out(self.local_steps - 1)
         if self.log_every and self.local_steps % self.log_every == 0:
             self.out("%d steps executed on worker %d." % (self.local_steps, self.task_id))
+
+    def any_rank(self, flag: bool) -> bool:
+        """True on every rank as soon as ``flag`` is true on one of them (collective; a no-op without a group)."""
+        if self.group is None:
+            return bool(flag)
+        import torch.distributed as dist
+
+        if dist.get_world_size(self.group) <= 1:
+            return bool(flag)
+        on_gpu = dist.get_backend(self.group) == "nccl"
+        t = torch.tensor([1.0 if flag else 0.0], device=getattr(self.engine, "device", "cpu") if on_gpu else "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return bool(t.item() > 0.0)
 
     def _agree(self, flag: bool) -> bool:
         """The chief's decision, known to every rank."""

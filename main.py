@@ -213,10 +213,24 @@ def train():
         saver = checkpointing.CheckpointSaver(FLAGS.train_dir, spec, opt.kind, save_secs=hp.save_checkpoint_secs,
                                               num_shards=max(1, cluster.num_ps), max_to_keep=hp.max_to_keep)
 
-    with trainer.MonitoredTrainingLoop(engine, source, hooks=hooks, is_chief=is_chief, saver=saver, task_id=role.task_id,
-                                       feeder=feeder, verbose_steps=FLAGS.verbose_steps, group=group) as sess:
-        while not sess.should_stop():
-            sess.run_step()
+    try:
+        with trainer.MonitoredTrainingLoop(engine, source, hooks=hooks, is_chief=is_chief, saver=saver, task_id=role.task_id,
+                                           feeder=feeder, verbose_steps=FLAGS.verbose_steps, group=group) as sess:
+            while not sess.should_stop():
+                sess.run_step()
+    except BaseException:
+        # leave the peers' mapped memory in an orderly way before the interpreter tears the CUDA context down
+        if use_cuda:
+            try:
+                torch.cuda.synchronize()
+            except Exception:
+                pass
+        if comm is not None:
+            try:
+                comm.close(collective=False)
+            except Exception:
+                pass
+        raise
     m = engine.metrics()
     print("final: global_step=%d loss=%.4f accuracy=%.3f" % (m["global_step"], m["total_loss"], m["accuracy"]))
 

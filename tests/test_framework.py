@@ -427,6 +427,10 @@ def test_convert_mnist_idx_to_png_to_tfrecord_roundtrip(tmp_path):
     assert [e["label"] for e in exs] == by_label
     first = np.frombuffer(exs[0]["image_raw"], np.uint8).reshape(28, 28, 3)
     assert np.array_equal(first[..., 0], first[..., 2])
+    rec2 = tmp_path / "train_space.tfrecord"      # the space-separated spelling of the same option
+    assert convert_mnist.main(["convert_mnist.py", "png2tfrecord", str(out / "training"), "--channels", "3", str(rec2)]) == 0
+    assert rec2.read_bytes() == rec.read_bytes()
+    assert convert_mnist.main(["convert_mnist.py", "png2tfrecord", str(out / "training"), str(rec2), "--channels", "2"]) == 2
     assert convert_mnist.main(["convert_mnist.py"]) == 2
 
 
