@@ -116,6 +116,21 @@ DTM_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {
   }
 }
 
+// Warp-wide wait for LONG waits (an epilogue warp waiting for the whole main loop, a builder warp waiting for the tensor
+// core to release a buffer): lane 0 polls with a sleep between polls, the other 31 lanes park at the warp barrier, so
+// that a waiting warp does not take issue slots from the MMA-issuing warp of the same scheduler.  Every lane must call
+// it (converged warp).
+DTM_DEVICE void mbar_wait_warp(uint64_t* bar, uint32_t parity, int tag = 0) {
+  if (lane_id() == 0 && !mbar_try_wait(bar, parity)) {
+    const long long t0 = clock64();
+    do {
+      __nanosleep(100);
+      if (clock64() - t0 > DTM_WATCHDOG_CYCLES) watchdog_trap("mbarrier wait (warp)", tag, (int)parity);
+    } while (!mbar_try_wait(bar, parity));
+  }
+  __syncwarp();
+}
+
 // ---------------------------------------------------------------------------------------------
 // TMA
 // ---------------------------------------------------------------------------------------------

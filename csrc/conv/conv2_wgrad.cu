@@ -118,7 +118,7 @@ conv2_wgrad_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __restr
     }
   } else if (warp >= 4) {
     const uint32_t q = warp & 3;
-    mbar_wait(&done_bar, 0, 32);
+    mbar_wait_warp(&done_bar, 0, 32);
     tc_fence_after();
     const int co = q * 16 + lane;  // valid for lane < 16
 #pragma unroll 1

@@ -23,6 +23,7 @@
 //
 // Work split: blockIdx.y halves the conv2 taps (13 | 12) as before; both halves walk the same images, and the conv1 part
 // of image iteration `it` is done by the half with the lighter tap group on even, the heavier on odd iterations.
+#include <stdlib.h>
 #include "../common/ptx.cuh"
 #include "../common/host_util.h"
 #include "../../include/dtm_b200.h"
@@ -75,7 +76,7 @@ __global__ void __launch_bounds__(256, 1)
 conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __restrict__ dz2_planes,
                         const uint8_t* __restrict__ x_u8, const __nv_bfloat16* __restrict__ grad_pooled,
                         const uint8_t* __restrict__ argmax, int batch, float* __restrict__ dw2, float* __restrict__ dw1,
-                        float* __restrict__ db1) {
+                        float* __restrict__ db1, int conv1_on) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[FW_STAGES], empty_bar[FW_STAGES], done_bar, c1_full, c1_empty;
   __shared__ uint32_t tmem_slot;
@@ -92,12 +93,12 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
   const int first = blockIdx.x, stride = gridDim.x;
   const int n_it = (batch - first + stride - 1) / stride;
   // conv1 images of this CTA: iterations with (it & 1) != y  (y = 1, the 12-tap group, takes the even ones)
-  const int n_c1 = y == 1 ? (n_it + 1) / 2 : n_it / 2;
+  const int n_c1 = !conv1_on ? 0 : (y == 1 ? (n_it + 1) / 2 : n_it / 2);
 
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < FW_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     mbar_init(&done_bar, 1);
-    mbar_init(&c1_full, FW_BUILDERS);
+    mbar_init(&c1_full, FW_BUILDERS / 32);
     mbar_init(&c1_empty, 1);
     fence_mbar_init();
   }
@@ -161,14 +162,16 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
         if (it == 0) fw_issue_conv2<true>(tmem_base, dz_base, p1_base, tap0, ntaps, idesc);
         else         fw_issue_conv2<false>(tmem_base, dz_base, p1_base, tap0, ntaps, idesc);
         umma_commit(&empty_bar[s]);
-        if ((it & 1) != y) {
+        if (conv1_on && (it & 1) != y) {
           mbar_wait(&c1_full, j & 1, 33);
           tc_fence_after();
+          if (!(conv1_on & 2)) {
           if (j == 0) umma_f16_c<false>(tmem_c1, umma_desc_at(e_base, 0), umma_desc_at(z1_base, 0), idesc);
           else        umma_f16_c<true>(tmem_c1, umma_desc_at(e_base, 0), umma_desc_at(z1_base, 0), idesc);
 #pragma unroll 5
           for (int i = 1; i < FW_C1_STEPS; ++i)
             umma_f16_c<true>(tmem_c1, umma_desc_at(e_base, i * 256), umma_desc_at(z1_base, i * 256), idesc);
+          }
           umma_commit(&c1_empty);
           ++j;
         }
@@ -180,7 +183,7 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
     const int bt = threadIdx.x - 64;        // 0..191
     int it = 0, j = 0;
     for (int img = first; img < batch; img += stride, ++it) {
-      if ((it & 1) == y) continue;
+      if (!conv1_on || (it & 1) == y) continue;
       // global loads of this image first: they are in flight while the previous conv1 image's MMAs are awaited
       const uint8_t* xs = x_u8 + static_cast<size_t>(img) * 784;
       uint32_t xw[2] = {0, 0};
@@ -199,7 +202,8 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
           av[k] = *reinterpret_cast<const uint2*>(as + pp * FW_C1 + cg * 8);
         }
       }
-      mbar_wait(&c1_empty, (j & 1) ^ 1, 34);
+      mbar_wait_warp(&c1_empty, (j & 1) ^ 1, 34);
+      if (conv1_on & 4) { fence_proxy_async_smem(); __syncwarp(); if (lane == 0) mbar_arrive(&c1_full); ++j; continue; }
       // 1. halo image in bf16: Xp[r + 2][c + 2] = x[r][c] / 255 - 0.5
       {
         auto put4 = [&](int word, uint32_t v) {
@@ -248,15 +252,16 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
           }
         }
       }
-      fence_proxy_async_smem();
-      mbar_arrive(&c1_full);
+      fence_proxy_async_smem();      // every writing lane, then one arrival per warp
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&c1_full);
       asm volatile("bar.sync 1, 192;" ::: "memory");     // nobody still reads the halo image when the next one is staged
       ++j;
     }
     if (warp >= 4) {
       // ------------------------------ epilogue ------------------------------
       const uint32_t q = warp & 3;
-      mbar_wait(&done_bar, 0, 32);
+      mbar_wait_warp(&done_bar, 0, 32);
       tc_fence_after();
       const int row = q * 16 + lane;  // accumulator row (M = 64: lanes 0-15 of each quadrant), valid for lane < 16
 #pragma unroll 1
@@ -271,17 +276,24 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
         }
       }
       if (n_c1 > 0) {
+        // conv1 accumulator: a lane holds one row (= one filter tap) x 32 channels.  Adding it from here would make every
+        // red.add instruction touch 16 different cache lines, and all CTAs of the grid add into the same 26 lines - the L2
+        // serialises ~4.5 K requests per line (measured: +10 us).  Transposed through shared memory a warp adds one tap row
+        // as a single 128-byte request: 26 requests per CTA.
         uint32_t r[32];
         tmem_ld_x32(tmem_base + ((q * 32u) << 16) + ntaps * FW_CI, r);
         tmem_ld_wait();
-        const int kh = row >> 3, kw = row & 7;
-        if (lane < 16 && kh < 5 && kw < 5) {
-          float* dst = dw1 + (kh * 5 + kw) * FW_C1;
+        float* s_red = reinterpret_cast<float*>(s_e);     // [64][33]; the entry buffer is idle once done_bar has fired
+        if (lane < 16) {
 #pragma unroll
-          for (int c = 0; c < FW_C1; ++c) red_add_f32(dst + c, __uint_as_float(r[c]));
-        } else if (lane < 16 && row == 5) {
-#pragma unroll
-          for (int c = 0; c < FW_C1; ++c) red_add_f32(db1 + c, __uint_as_float(r[c]));
+          for (int c = 0; c < FW_C1; ++c) s_red[row * 33 + c] = __uint_as_float(r[c]);
+        }
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+        for (int m = q; m < 64; m += 4) {
+          const int kh = m >> 3, kw = m & 7;
+          const float v = s_red[m * 33 + lane];
+          if (kh < 5 && kw < 5) red_add_f32(dw1 + (kh * 5 + kw) * FW_C1 + lane, v);
+          else if (m == 5)      red_add_f32(db1 + lane, v);
         }
       }
     }
@@ -301,6 +313,10 @@ extern "C" int dtm_conv_wgrad_fused(const void* p1_planes, const void* dz2_plane
   if (!p1_planes || !dz2_planes || !x_u8 || !grad_pooled || !argmax || !dw2 || !dw1 || !db1)
     return dtm_fail("conv_wgrad_fused: null argument");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // experiment switch (tools/kernel_bench.py): DTM_FW_NO_CONV1=1 leaves the conv1 part out (dw1 / db1 stay untouched)
+  const char* e = getenv("DTM_FW_NO_CONV1");
+  // (values 3 / 5 / 7: conv1 pipeline without its MMAs / without the operand building / without both - timing only)
+  const int conv1_on = e ? ((e[0] == '1') ? 0 : atoi(e)) : 1;
   static bool configured = false;
   if (!configured) {
     DTM_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FW_SMEM));
@@ -309,7 +325,8 @@ extern "C" int dtm_conv_wgrad_fused(const void* p1_planes, const void* dz2_plane
   const int gx = min(batch, max(1, device_sm_count() / 2));
   DTM_CUDA_OK(launch_pdl(conv_wgrad_fused_kernel, dim3(gx, 2), dim3(256), FW_SMEM, s, static_cast<const uint8_t*>(p1_planes),
                          static_cast<const uint8_t*>(dz2_planes), static_cast<const uint8_t*>(x_u8),
-                         static_cast<const __nv_bfloat16*>(grad_pooled), static_cast<const uint8_t*>(argmax), batch, dw2, dw1, db1));
+                         static_cast<const __nv_bfloat16*>(grad_pooled), static_cast<const uint8_t*>(argmax), batch, dw2, dw1, db1,
+                         conv1_on));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

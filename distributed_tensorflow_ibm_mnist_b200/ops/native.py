@@ -51,6 +51,7 @@ class TrainState(ctypes.Structure):
         ("wl_sum", c_float * MAX_SEGMENTS),
         ("last_wl", c_float * MAX_SEGMENTS),
         ("loss_avg", c_float * (MAX_SEGMENTS + 2)),
+        ("work", ctypes.c_uint), ("reserved0", ctypes.c_uint),
     ]
 
 

@@ -51,6 +51,8 @@ typedef struct dtm_train_state {
   float wl_sum[DTM_MAX_SEGMENTS];   /* sum of squares per variable (weights used by the step in flight)   */
   float last_wl[DTM_MAX_SEGMENTS];  /* wd * l2_loss per variable of the last completed step               */
   float loss_avg[DTM_MAX_SEGMENTS + 2]; /* EMA(0.9): per-variable weight_loss, [16] cross_entropy, [17] total_loss */
+  unsigned int work;       /* internal: chunk dispenser of dtm_fused_update_range (zero between launches)         */
+  unsigned int reserved0;
 } dtm_train_state;
 
 /* Flat parameter space: variables ("segments") are laid out back to back, each offset a multiple of 64 elements. */
