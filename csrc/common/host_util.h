@@ -31,6 +31,14 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64
 
 int device_sm_count();
 
+// Access-policy window the optimizer update kernels are launched with (dtm_set_update_l2_window); null when off.
+struct L2Window {
+  void* base = nullptr;
+  size_t bytes = 0;
+  float hit_ratio = 0.0f;
+};
+const L2Window* update_l2_window();
+
 // Programmatic dependent launch mode: 0 off (every kernel starts after its predecessor has drained), 1 strict, 2 early
 // weights (see runtime.cu).  DTM_PDL=0|1|2 in the environment, or dtm_set_pdl_mode().
 int pdl_mode();

@@ -168,12 +168,24 @@ extern "C" int dtm_fused_update_range(const dtm_update_config* cfg, dtm_train_st
   if (grid < 1) grid = 1;
   if (cfg->pack_seg >= cfg->n_segments || (cfg->pack_seg >= 0 && (!cfg->pack_fwd || !cfg->pack_dgrad)))
     return dtm_fail("fused_update: pack_seg set without both pack buffers");
-  if (dynamic)
-    fused_update_kernel<<<grid, 256, 0, s>>>(*cfg, state, w, grad, slot0, slot1, ema, static_cast<__nv_bfloat16*>(w_bf16),
-                                             grad_scale, lo, hi, do_finish);
-  else
-    fused_update_stride_kernel<<<grid, 256, 0, s>>>(*cfg, state, w, grad, slot0, slot1, ema, static_cast<__nv_bfloat16*>(w_bf16),
-                                                    grad_scale, lo, hi, do_finish);
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = dim3(grid);
+  lc.blockDim = dim3(256);
+  lc.stream = s;
+  cudaLaunchAttribute attr[1];
+  if (const L2Window* win = update_l2_window()) {   // optimizer state stays in the persisting L2 between steps
+    attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
+    attr[0].val.accessPolicyWindow.base_ptr = win->base;
+    attr[0].val.accessPolicyWindow.num_bytes = win->bytes;
+    attr[0].val.accessPolicyWindow.hitRatio = win->hit_ratio;
+    attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr[0].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+  }
+  __nv_bfloat16* wb = static_cast<__nv_bfloat16*>(w_bf16);
+  if (dynamic) DTM_CUDA_OK(cudaLaunchKernelEx(&lc, fused_update_kernel, *cfg, state, w, grad, slot0, slot1, ema, wb, grad_scale, lo, hi, do_finish));
+  else         DTM_CUDA_OK(cudaLaunchKernelEx(&lc, fused_update_stride_kernel, *cfg, state, w, grad, slot0, slot1, ema, wb, grad_scale, lo, hi, do_finish));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

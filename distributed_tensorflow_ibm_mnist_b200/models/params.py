@@ -30,6 +30,18 @@ class FlatParams:
             self.index[v.name] = i
             off += _align(v.size)
         self.total = off
+        self.blob = None
+        if allocator is None and with_slots >= 2 and with_ema:
+            # one contiguous allocation [w | grad | slot0 | slot1 | ema | w_bf16]: a single address range that the update
+            # kernels can keep in the persisting L2 (native.set_update_l2_window)
+            self.blob = torch.zeros(self.total * 22, dtype=torch.uint8, device=self.device)
+            order = {"w": 0, "grad": 1, "slot0": 2, "slot1": 3, "ema": 4}
+
+            def allocator(n, dtype, name=""):   # noqa: E306
+                if name == "w_bf16":
+                    return self.blob[self.total * 20:].view(torch.bfloat16)
+                k = order[name]
+                return self.blob[self.total * 4 * k:self.total * 4 * (k + 1)].view(torch.float32)
         alloc = allocator or (lambda n, dtype, name="": torch.zeros(n, dtype=dtype, device=self.device))
         self.w = alloc(self.total, torch.float32, "w")
         self.grad = alloc(self.total, torch.float32, "grad")

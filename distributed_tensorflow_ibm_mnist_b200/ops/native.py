@@ -33,6 +33,7 @@ _lib.register("dtm_head_forward", [P, I, I, P, P, P, F, F, P, P, P, P, F, P, P])
 _lib.register("dtm_head_backward", [P, I, I, P, P, F, P, P, P, P, I, P])
 _lib.register("dtm_fused_update", [P, P, P, P, P, P, P, P, F, P])
 _lib.register("dtm_fused_update_range", [P, P, P, P, P, P, P, P, F, I, I, I, I, P])
+_lib.register("dtm_set_update_l2_window", [P, ctypes.c_size_t, P, P])
 _lib.register("dtm_state_init", [P, c_longlong, F, F, P])
 _lib.register("dtm_tensor_stats_scratch_bytes", [ctypes.c_size_t], ctypes.c_size_t)
 _lib.register("dtm_tensor_stats", [P, ctypes.c_size_t, I, P, P, ctypes.c_size_t, P])
@@ -188,6 +189,15 @@ def fused_update_range(cfg: UpdateConfig, state, w, grad, slot0, slot1, ema, w_b
                                       ptr(w_bf16), float(grad_scale), int(lo), int(hi), int(finish), int(max_ctas),
                                       current_stream()),
           "fused_update_range")
+
+
+def set_update_l2_window(blob: torch.Tensor | None) -> dict:
+    """Launch the optimizer update kernels of the current device with a persisting-L2 window over ``blob`` (the contiguous
+    optimizer state); ``None`` switches it off.  Returns the carve-out and the window limit of the device."""
+    carve, win = ctypes.c_size_t(0), ctypes.c_size_t(0)
+    nbytes = 0 if blob is None else blob.numel() * blob.element_size()
+    check(_L().dtm_set_update_l2_window(ptr(blob), nbytes, ctypes.byref(carve), ctypes.byref(win)), "set_update_l2_window")
+    return {"bytes": nbytes, "carveout_bytes": carve.value, "max_window_bytes": win.value}
 
 
 def state_init(state, global_step=0, beta1=0.9, beta2=0.999):

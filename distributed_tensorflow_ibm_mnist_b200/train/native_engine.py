@@ -55,6 +55,15 @@ class NativeEngine:
         self.cfg.pack_seg = self.flat.index["conv2/weights"]
         self.cfg.pack_fwd = self.w2_fwd.data_ptr()
         self.cfg.pack_dgrad = self.w2_dgrad.data_ptr()
+        # single GPU: the whole optimizer state (72 MB for the baseline preset) lives in the persisting part of the 126 MB L2
+        # (measured, same box: 159.8 -> 157.6 us per step with the separate weight-gradient kernels, 162.4 -> 152.6 with the
+        # fused one; DTM_L2_PERSIST=0 switches it off)
+        self.l2_window = None
+        if self.flat.blob is not None and os.environ.get("DTM_L2_PERSIST", "1") != "0":
+            try:
+                self.l2_window = native.set_update_l2_window(self.flat.blob)
+            except _lib.NativeError:
+                self.l2_window = None
         self._graphs: dict[int, torch.cuda.CUDAGraph] = {}
         self._side = torch.cuda.Stream(device=self.device)
         self._comm_stream = torch.cuda.Stream(device=self.device)
@@ -92,9 +101,9 @@ class NativeEngine:
             # 32 CTAs reach the time of 148) - leave most SMs entirely to the conv backward
             comm.overlap_ctas = 64
         # one tcgen05 kernel for both convolution weight gradients (conv1's operands are built by the warps that idle in
-        # conv2_wgrad): single-channel uint8 input only.  Opt-in (DTM_WGRAD_FUSED=1) until it beats the two separate
-        # kernels inside the step (first measurement: 171 vs 161 us per step)
-        self._fused_wgrad = spec.channels == 1 and env.get("DTM_WGRAD_FUSED", "0") == "1"
+        # conv2_wgrad): single-channel uint8 input only; DTM_WGRAD_FUSED=0 restores the two separate kernels.  Pays off
+        # together with the persisting-L2 optimizer state (profiles/ab_wgrad_update_r2.md): 152.6 vs 157.6 us per step
+        self._fused_wgrad = spec.channels == 1 and env.get("DTM_WGRAD_FUSED", "1") != "0"
         # experiment switches (tools/ablate.py): kernels to leave out of the step (timing only - results are then wrong) and
         # a flag that puts every kernel on the main stream
         self._skip = set(filter(None, env.get("DTM_SKIP", "").split(",")))

@@ -96,6 +96,11 @@ typedef struct dtm_peer_ctx {
 } dtm_peer_ctx;
 
 /* ---- runtime ---------------------------------------------------------------------------------- */
+/* Keep [base, base + bytes) - the flat optimizer state - in the persisting part of the L2 for the update kernels of the
+ * current device (access-policy window on their launches; the carve-out is raised to min(bytes, device maximum)).
+ * base = NULL switches it off.  The reference has no counterpart (its Apply ops run inside TensorFlow's runtime,
+ * mnist_input.py:262-264); this is a B200 memory-hierarchy decision. */
+int dtm_set_update_l2_window(const void* base, size_t bytes, size_t* carveout_bytes, size_t* max_window_bytes);
 const char* dtm_last_error(void);
 int dtm_abi_version(void);
 int dtm_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin);
