@@ -74,10 +74,14 @@ DTM_DEVICE void mc_st_v4(float* p, float4 v) {
 DTM_DEVICE void mc_st_bf16x4(__nv_bfloat16* p, uint32_t a, uint32_t b) {
   asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(p), "r"(a), "r"(b) : "memory");
 }
+DTM_DEVICE void mc_st_bf16x8(__nv_bfloat16* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
 
 // Ranks may reach a collective seconds apart (start-up, graph capture), so cross-GPU waits get a longer leash than
 // the intra-kernel pipelines: ~2 minutes of SM clocks.
-constexpr long long COMM_WATCHDOG_CYCLES = 240000000000ll;
+__device__ long long g_comm_watchdog_cycles = 240000000000ll;   // dtm_set_comm_watchdog() overrides it (tests: seconds, not minutes)
+#define COMM_WATCHDOG_CYCLES g_comm_watchdog_cycles
 
 DTM_DEVICE void spin_until_ge_sys(const unsigned int* p, unsigned int target, int tag) {
   const long long t0 = clock64();
@@ -90,32 +94,38 @@ DTM_DEVICE void spin_until_ge_gpu(const unsigned int* p, unsigned int target, in
     if (clock64() - t0 > COMM_WATCHDOG_CYCLES) watchdog_trap("grid barrier", tag, (int)target);
 }
 
-// All CTAs of the kernel on all ranks rendezvous; `k` is the epoch value to publish (strictly increasing).
-DTM_DEVICE void cross_gpu_barrier(const dtm_peer_ctx& ctx, CommCtrl* ctrl, unsigned int k) {
+// Two rendezvous flavours over the same epoch flags (`k` strictly increasing; slot r of every rank is written by rank r).
+//
+// barrier_ready  - "everything the kernels in front of this one wrote on rank r is visible": nothing of THIS kernel has to
+//                  be waited for, so CTA 0 publishes at once and every CTA polls its own rank's flags (local memory) by
+//                  itself - one NVLink store latency, no grid-wide arrive, no release broadcast.
+// barrier_done   - "every CTA of this kernel on every rank has finished its peer loads and stores": CTAs count in, the
+//                  last one publishes to the peers, and again every CTA polls the local flags itself.
+// Kernels are launched cooperatively so that all CTAs are co-resident while they spin.
+DTM_DEVICE void barrier_ready_publish(const dtm_peer_ctx& ctx, unsigned int k) {
+  if (blockIdx.x == 0 && threadIdx.x < ctx.world) st_release_sys(ctx.flags[threadIdx.x] + ctx.rank, k);
+}
+DTM_DEVICE void barrier_ready_wait(const dtm_peer_ctx& ctx, unsigned int k) {
+  if (threadIdx.x < ctx.world) spin_until_ge_sys(ctx.flags[ctx.rank] + threadIdx.x, k, threadIdx.x);
   __syncthreads();
-  if (blockIdx.x == 0) {
-    if (threadIdx.x == 0) {
-      __threadfence_system();
-      if (gridDim.x > 1) {
-        const long long t0 = clock64();
-        while (ld_acquire_gpu(&ctrl->arrive) != gridDim.x - 1)
-          if (clock64() - t0 > COMM_WATCHDOG_CYCLES) watchdog_trap("grid arrive", (int)k, 0);
-        ctrl->arrive = 0;
-        __threadfence();
-      }
-    }
-    __syncthreads();
-    if (threadIdx.x < ctx.world) {
-      st_release_sys(ctx.flags[threadIdx.x] + ctx.rank, k);
-      spin_until_ge_sys(ctx.flags[ctx.rank] + threadIdx.x, k, threadIdx.x);
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) st_release_gpu(&ctrl->go, k);
-  } else if (threadIdx.x == 0) {
+}
+DTM_DEVICE void barrier_ready(const dtm_peer_ctx& ctx, unsigned int k) {
+  barrier_ready_publish(ctx, k);
+  barrier_ready_wait(ctx, k);
+}
+DTM_DEVICE void barrier_done(const dtm_peer_ctx& ctx, CommCtrl* ctrl, unsigned int k) {
+  __shared__ unsigned int s_publish;
+  __syncthreads();
+  if (threadIdx.x == 0) {
     __threadfence_system();
-    red_release_gpu_add(&ctrl->arrive, 1u);
-    spin_until_ge_gpu(&ctrl->go, k, 1);
+    unsigned int prev;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(&ctrl->arrive) : "memory");
+    s_publish = prev == gridDim.x - 1 ? 1u : 0u;
+    if (s_publish) ctrl->arrive = 0;   // nobody counts in again before this barrier has released them
   }
+  __syncthreads();
+  if (s_publish && threadIdx.x < ctx.world) st_release_sys(ctx.flags[threadIdx.x] + ctx.rank, k);
+  if (threadIdx.x < ctx.world) spin_until_ge_sys(ctx.flags[ctx.rank] + threadIdx.x, k, threadIdx.x);
   __syncthreads();
 }
 
@@ -169,7 +179,10 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
                               float* __restrict__ ema, __nv_bfloat16* __restrict__ w_bf16, CommCtrl* __restrict__ ctrl,
                               int do_finish, int depth) {
   const int N = ctx.world, r = ctx.rank;
+  pdl_wait();                 // launched with a programmatic edge: the launch latency hides under the preceding kernel's tail
+  pdl_launch_dependents();
   const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
+  barrier_ready_publish(ctx, e0 + 1);      // my gradients are complete: tell the peers before anything else
   const UpdateScalars u = make_update_scalars(cfg, st, 1.0f / static_cast<float>(N));
   float* w_local = ctx.w[r];
   float* g_local = ctx.grad[r];
@@ -211,15 +224,17 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   }
 
   // ---- barrier A: every rank's gradients are complete
-  cross_gpu_barrier(ctx, ctrl, e0 + 1);
+  barrier_ready_wait(ctx, e0 + 1);
 
   // ---- reduce-scatter + optimizer on my shard + all-gather of the new weights
   int s_lo, s_hi;
   shard_range(lo, hi, r, N, s_lo, s_hi);
   constexpr bool nvls = NVLS;
   int seg = 0;
-  // optimizer + EMA on one float4 of my shard, then publish it: multicast store (NVLS) or N-1 peer stores (P2P)
-  auto apply = [&](int i, const float4 g) {
+  // optimizer + EMA on one float4 of my shard, then publish it: multicast store (NVLS) or N-1 peer stores (P2P).  With
+  // `defer_bf16` the packed bf16 value of a tensor-core-only variable is handed back instead of stored (the NVLS loop pairs
+  // two neighbouring float4 into one 16-byte multicast store).
+  auto apply = [&](int i, const float4 g, bool defer_bf16, uint2& pk_out) -> bool {
     seg = segment_advance(cfg, seg, i);
     const float wd = cfg.seg_wd[seg];
     const float4 wv = *reinterpret_cast<const float4*>(w_local + i);
@@ -229,6 +244,7 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
       // tensor-core-only variable: peers need the bf16 value, nothing else (half the link bytes, no conversion pass)
       const uint2 pk = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
       if (nvls) {
+        if (defer_bf16) { pk_out = pk; return true; }
         mc_st_bf16x4(static_cast<__nv_bfloat16*>(ctx.mc_w_bf16) + i, pk.x, pk.y);
       } else {
 #pragma unroll 1
@@ -246,20 +262,32 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
         st_peer_v4(ctx.w[p] + i, o);
       }
     }
+    return false;
   };
   const int step = nthreads * 4;
   if (nvls) {
-    // `depth` (<= U) in-switch reductions in flight per thread before the first one is consumed
-    constexpr int U = LIGHT ? 2 : 4;
-    depth = LIGHT ? (depth > U ? U : depth) : U;
-    for (int base = s_lo + tid * 4; base < s_hi; base += step * depth) {
-      float4 g[U];
+    // a thread owns 8 consecutive elements per visit (shard and segment borders are multiples of 64): two in-switch
+    // reductions in flight per visit, U visits in flight, and ONE 16-byte multicast store of the packed bf16 weights
+    constexpr int U = LIGHT ? 1 : 2;
+    const int nvis = LIGHT ? 1 : (depth >= 2 ? 2 : 1);
+    const int step8 = nthreads * 8;
+    for (int base = s_lo + tid * 8; base < s_hi; base += step8 * nvis) {
+      float4 g[2 * U];
 #pragma unroll
       for (int k = 0; k < U; ++k)
-        if (k < depth && base + k * step < s_hi) g[k] = mc_ld_reduce_v4(ctx.mc_grad + base + k * step);
+        if (k < nvis && base + k * step8 < s_hi) {
+          g[2 * k] = mc_ld_reduce_v4(ctx.mc_grad + base + k * step8);
+          g[2 * k + 1] = mc_ld_reduce_v4(ctx.mc_grad + base + k * step8 + 4);
+        }
 #pragma unroll
       for (int k = 0; k < U; ++k)
-        if (k < depth && base + k * step < s_hi) apply(base + k * step, g[k]);
+        if (k < nvis && base + k * step8 < s_hi) {
+          const int i = base + k * step8;
+          uint2 p0 = make_uint2(0, 0), p1 = make_uint2(0, 0);
+          const bool d0 = apply(i, g[2 * k], true, p0);
+          apply(i + 4, g[2 * k + 1], true, p1);
+          if (d0) mc_st_bf16x8(static_cast<__nv_bfloat16*>(ctx.mc_w_bf16) + i, p0.x, p0.y, p1.x, p1.y);
+        }
     }
   } else if (N == 8 || N == 4 || N == 2) {
     // two float4 per thread and iteration: 2(N-1) NVLink round trips overlap, and the second one hides the optimizer
@@ -269,15 +297,16 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
       const float4 g0 = reduce_peers(ctx.grad, N, base);
       float4 g1 = make_float4(0.f, 0.f, 0.f, 0.f);
       if (two) g1 = reduce_peers(ctx.grad, N, base + step);
-      apply(base, g0);
-      if (two) apply(base + step, g1);
+      uint2 unused;
+      apply(base, g0, false, unused);
+      if (two) apply(base + step, g1, false, unused);
     }
   } else {
-    for (int i = s_lo + tid * 4; i < s_hi; i += step) apply(i, reduce_peers(ctx.grad, N, i));
+    for (int i = s_lo + tid * 4; i < s_hi; i += step) { uint2 unused; apply(i, reduce_peers(ctx.grad, N, i), false, unused); }
   }
 
   // ---- barrier B: all shards of the new weights have landed everywhere, nobody reads my gradients any more
-  cross_gpu_barrier(ctx, ctrl, e0 + 2);
+  barrier_done(ctx, ctrl, e0 + 2);
 
   // ---- local pass, only over the variables that were gathered in fp32 (the small ones): bf16 shadow, operand images,
   //      and clearing of gradients that are accumulated with atomics
@@ -323,7 +352,7 @@ allreduce_kernel(const dtm_peer_ctx ctx, float* const* __restrict__ bufs, float*
   const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   const int nthreads = gridDim.x * blockDim.x;
-  cross_gpu_barrier(ctx, ctrl, e0 + 1);
+  barrier_ready(ctx, e0 + 1);
   const int step = nthreads * 4;
   if (mode == 0) {
     if (mc) {
@@ -361,7 +390,7 @@ allreduce_kernel(const dtm_peer_ctx ctx, float* const* __restrict__ bufs, float*
       }
     }
   }
-  cross_gpu_barrier(ctx, ctrl, e0 + 2);
+  barrier_done(ctx, ctrl, e0 + 2);
   if (mode == 1 && out != bufs[r] + off)
     for (int i = tid * 4; i < n; i += nthreads * 4)
       *reinterpret_cast<float4*>(out + i) = *reinterpret_cast<const float4*>(bufs[r] + off + i);
@@ -379,29 +408,42 @@ broadcast_kernel(const dtm_peer_ctx ctx, float* const* __restrict__ bufs, int of
   const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   const int nthreads = gridDim.x * blockDim.x;
-  cross_gpu_barrier(ctx, ctrl, e0 + 1);
+  barrier_ready(ctx, e0 + 1);
   if (r != root)
     for (int i = tid * 4; i < n; i += nthreads * 4)
       *reinterpret_cast<float4*>(bufs[r] + off + i) = ld_peer_v4(bufs[root] + off + i);
-  cross_gpu_barrier(ctx, ctrl, e0 + 2);
+  barrier_done(ctx, ctrl, e0 + 2);
   __shared__ unsigned int s_last;
   if (threadIdx.x == 0) { __threadfence(); s_last = (atomicAdd(&ctrl->ticket, 1u) == gridDim.x - 1) ? 1u : 0u; }
   __syncthreads();
   if (s_last && threadIdx.x == 0) { ctrl->ticket = 0; st_release_gpu(&ctrl->epoch, e0 + 2); }
 }
 
+// Cooperative launch (all CTAs co-resident: they spin on each other).  With `pdl` the launch also carries the programmatic
+// stream-serialization attribute, so that the kernel is scheduled while its predecessor drains; should the driver refuse the
+// combination, the first refusal switches it off for good.
 template <typename Kernel, typename... Args>
-static int launch_cooperative(Kernel kern, int grid, int block, cudaStream_t s, Args... args) {
+static int launch_cooperative(Kernel kern, int grid, int block, cudaStream_t s, bool pdl, Args... args) {
+  static bool pdl_ok = true;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(block);
   cfg.dynamicSmemBytes = 0;
   cfg.stream = s;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeCooperative;
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  if (pdl && pdl_ok && pdl_enabled()) {
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.numAttrs = 2;
+    if (cudaLaunchKernelEx(&cfg, kern, args...) == cudaSuccess) return 0;
+    (void)cudaGetLastError();
+    pdl_ok = false;
+    cfg.numAttrs = 1;
+  }
   DTM_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, args...));
   return 0;
 }
@@ -415,10 +457,11 @@ static int comm_grid(size_t elems, int max_ctas = 0, int threads = 512) {
   return static_cast<int>(want > static_cast<size_t>(cap) ? cap : want);
 }
 
-// in-flight multimem.ld_reduce per thread in the fused exchange (tuning knob, DTM_COMM_DEPTH=1..8)
+// visits (8 elements = two multimem.ld_reduce) in flight per thread in the heavy NVLS instantiation: DTM_COMM_DEPTH = 1 | 2
+// (values above 2 are clamped - the round-1 8-GPU sweep found 4 and 8 slower; the light instantiation always uses 1)
 static int comm_depth() {
   const char* e = getenv("DTM_COMM_DEPTH");   // read per launch (cheap) so that tools can sweep it inside one process
-  const int v = e ? atoi(e) : 2;   // 8-GPU sweep (profiles/fused_exchange_8gpu_sweep_r1.json): 1-2 best, 8 worst
+  const int v = e ? atoi(e) : 2;
   return v < 1 ? 1 : (v > 2 ? 2 : v);
 }
 
@@ -463,6 +506,13 @@ extern "C" int dtm_symm_free(void* ptr) {
   return 0;
 }
 
+extern "C" int dtm_set_comm_watchdog(long long cycles) {
+  using namespace dtm;
+  if (cycles <= 0) return dtm_fail("comm watchdog: cycles must be positive");
+  DTM_CUDA_OK(cudaMemcpyToSymbol(g_comm_watchdog_cycles, &cycles, sizeof(cycles)));
+  return 0;
+}
+
 // ---- collectives ------------------------------------------------------------------------------------------
 extern "C" int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_update_config* cfg, dtm_train_state* state,
                                           int lo, int hi, float* slot0, float* slot1, float* ema, void* w_bf16, void* ctrl,
@@ -478,14 +528,14 @@ extern "C" int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_upd
   const bool light = static_cast<size_t>(hi - lo) / ctx->world <= (2u << 20);
   if (nvls && light)
     return launch_cooperative(fused_allreduce_update_kernel<true, true>, comm_grid(static_cast<size_t>(hi - lo), max_ctas, 256), 256,
-                              static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
+                              static_cast<cudaStream_t>(stream), true, *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
                               static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
   if (nvls)
     return launch_cooperative(fused_allreduce_update_kernel<true, false>, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
-                              static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
+                              static_cast<cudaStream_t>(stream), true, *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
                               static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
   return launch_cooperative(fused_allreduce_update_kernel<false, false>, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
-                            static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
+                            static_cast<cudaStream_t>(stream), true, *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
                             static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
 }
 
@@ -496,7 +546,7 @@ extern "C" int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev
   if (n <= 0 || n % 4 || off % 4) return dtm_fail("allreduce: n and offset must be positive multiples of 4");
   if (mode != 0 && mode != 1) return dtm_fail("allreduce: mode 0 (one-shot) or 1 (two-shot)");
   const size_t work = mode == 0 ? static_cast<size_t>(n) : static_cast<size_t>(n) / ctx->world + 1;
-  return launch_cooperative(allreduce_kernel, comm_grid(work), 512, static_cast<cudaStream_t>(stream), *ctx, bufs_dev, mc_buf, off, n,
+  return launch_cooperative(allreduce_kernel, comm_grid(work), 512, static_cast<cudaStream_t>(stream), false, *ctx, bufs_dev, mc_buf, off, n,
                             out, mode, static_cast<CommCtrl*>(ctrl));
 }
 
@@ -505,6 +555,6 @@ extern "C" int dtm_broadcast_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev
   if (int rc = check_ctx(ctx)) return rc;
   if (n <= 0 || n % 4 || off % 4) return dtm_fail("broadcast: n and offset must be positive multiples of 4");
   if (root < 0 || root >= ctx->world) return dtm_fail("broadcast: bad root");
-  return launch_cooperative(broadcast_kernel, comm_grid(static_cast<size_t>(n)), 512, static_cast<cudaStream_t>(stream), *ctx,
+  return launch_cooperative(broadcast_kernel, comm_grid(static_cast<size_t>(n)), 512, static_cast<cudaStream_t>(stream), false, *ctx,
                             bufs_dev, off, n, root, static_cast<CommCtrl*>(ctrl));
 }

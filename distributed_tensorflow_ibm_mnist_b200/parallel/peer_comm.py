@@ -30,6 +30,7 @@ _lib.register("dtm_symm_free", [P])
 _lib.register("dtm_fused_allreduce_update", [P, P, P, I, I, P, P, P, P, P, I, I, P])
 _lib.register("dtm_allreduce_f32", [P, P, P, I, I, P, I, P, P])
 _lib.register("dtm_broadcast_f32", [P, P, I, I, I, P, P])
+_lib.register("dtm_set_comm_watchdog", [ctypes.c_longlong])
 
 
 class PeerCtx(ctypes.Structure):
@@ -145,6 +146,12 @@ class PeerComm:
         if self.world_size > MAX_RANKS:
             raise ValueError(f"PeerComm supports up to {MAX_RANKS} ranks on one NVSwitch node")
         torch.cuda.set_device(self.device)
+        # DTM_COMM_WATCHDOG_MS: how long a kernel waits for a peer before it traps with "[dtm watchdog] peer barrier (a rank
+        # did not arrive)" (default about two minutes; fault-injection tests use seconds)
+        ms = os.environ.get("DTM_COMM_WATCHDOG_MS")
+        if ms:
+            khz = torch.cuda.get_device_properties(self.device).clock_rate if hasattr(torch.cuda.get_device_properties(self.device), "clock_rate") else 1_965_000
+            check(_lib.load().dtm_set_comm_watchdog(int(float(ms) * khz)), "set_comm_watchdog")
         self.nvls = _nvls_available(group, self.device)   # in-switch reduction + multicast stores (multimem.*)
         # grid cap of a fused exchange that overlaps compute kernels.  NVLS kernel: 0 = one small CTA on every SM, co-resident
         # with the conv backward (2 GPUs: 222 -> 189 us per step against a 64-CTA cap); P2P kernel (512 threads, cannot

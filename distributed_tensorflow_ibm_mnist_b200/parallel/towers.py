@@ -13,6 +13,7 @@ import os
 import socket
 import subprocess
 import sys
+import time
 
 
 def _free_port() -> int:
@@ -21,19 +22,64 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-def launch_towers(num_gpus: int, argv: list[str], *, script: str) -> int:
-    ports = [_free_port() for _ in range(num_gpus)]
-    worker_hosts = ",".join(f"127.0.0.1:{p}" for p in ports)
+def _spawn(num_workers: int, argv: list[str], script: str, attempt: int) -> list[subprocess.Popen]:
     procs = []
-    for rank in range(num_gpus):
-        env = dict(os.environ, LOCAL_RANK=str(rank), RANK=str(rank), WORLD_SIZE=str(num_gpus))
+    if num_workers <= 1:     # one supervised worker in local mode
+        env = dict(os.environ, DTM_SUPERVISED="1", DTM_RESTART_COUNT=str(attempt))
+        return [subprocess.Popen([sys.executable, script, *argv], env=env)]
+    ports = [_free_port() for _ in range(num_workers)]
+    worker_hosts = ",".join(f"127.0.0.1:{p}" for p in ports)
+    for rank in range(num_workers):
+        env = dict(os.environ, LOCAL_RANK=str(rank), RANK=str(rank), WORLD_SIZE=str(num_workers), DTM_SUPERVISED="1",
+                   DTM_RESTART_COUNT=str(attempt))
         cmd = [sys.executable, script, *argv, "--job_name=worker", f"--task_id={rank}", f"--worker_hosts={worker_hosts}"]
         procs.append(subprocess.Popen(cmd, env=env))
-    rc = 0
+    return procs
+
+
+def _stop(procs: list[subprocess.Popen], grace_s: float = 5.0) -> None:
+    """Terminate exactly the processes this supervisor started (never by name pattern)."""
     for p in procs:
-        rc = p.wait() or rc
-    if rc:
-        for p in procs:
-            if p.poll() is None:
-                p.kill()
-    return rc
+        if p.poll() is None:
+            p.terminate()
+    t0 = time.time()
+    for p in procs:
+        try:
+            p.wait(timeout=max(0.1, grace_s - (time.time() - t0)))
+        except subprocess.TimeoutExpired:
+            p.kill()
+            p.wait()
+
+
+def launch_towers(num_gpus: int, argv: list[str], *, script: str, max_restarts: int = 0, poll_s: float = 0.2, out=print) -> int:
+    """Run ``num_gpus`` worker processes and supervise them: the process-level form of ``MonitoredTrainingSession``'s
+    recoverable session (reference main.py:140-146).
+
+    Synchronous replicas live and die together: when one worker exits with an error (a crash, a trapped kernel watchdog
+    after a peer vanished, a lost connection) the survivors cannot make progress, so the supervisor stops them, and - up
+    to ``max_restarts`` times - starts the whole set again.  Every new worker restores the newest checkpoint in
+    ``--train_dir`` (``restore-or-init`` in main.py), so training continues from the last saved global step with
+    bit-identical state.  ``DTM_RESTART_COUNT`` tells the workers which attempt they belong to."""
+    attempt = 0
+    while True:
+        procs = _spawn(num_gpus, argv, script, attempt)
+        failed = None
+        while failed is None and any(p.poll() is None for p in procs):
+            for k, p in enumerate(procs):
+                rc = p.poll()
+                if rc not in (None, 0):
+                    failed = (k, rc)
+                    break
+            if failed is None:
+                time.sleep(poll_s)
+        if failed is None:
+            failed = next(((k, p.returncode) for k, p in enumerate(procs) if p.returncode), None)
+        if failed is None:
+            return 0
+        _stop(procs)
+        if attempt >= max_restarts:
+            out(f"[supervisor] worker {failed[0]} exited with status {failed[1]}; no restarts left ({attempt} used)")
+            return failed[1] if failed[1] > 0 else 1
+        attempt += 1
+        out(f"[supervisor] worker {failed[0]} exited with status {failed[1]}; restarting all {max(1, num_gpus)} worker(s) from the "
+            f"newest checkpoint (restart {attempt} of {max_restarts})")

@@ -76,6 +76,30 @@ class NanLossHook(Hook):
         self._check(loop)
 
 
+class FaultInjectionHook(Hook):
+    """Test hook for the failure path: ``DTM_FAULT_INJECT="<rank>:<local step>[:<attempt>]"`` makes that worker
+    die abruptly (``os._exit(43)``: no clean-up, no goodbye to its peers - what a crashed process looks like) after that
+    many local steps, on that restart attempt (default 0, the first run) of a supervised job."""
+
+    EXIT_CODE = 43
+
+    def __init__(self, spec: str, rank: int, attempt: int, out=print):
+        parts = [int(x) for x in spec.split(":")]
+        self.rank, self.step = parts[0], parts[1]
+        self.attempt = parts[2] if len(parts) > 2 else 0
+        self.active = rank == self.rank and attempt == self.attempt
+        self.out = out
+
+    def after_run(self, ctx: RunContext) -> None:
+        if self.active and ctx.loop.local_steps >= self.step:
+            import os
+            import sys
+
+            self.out(f"[fault-injection] worker {self.rank} dies after local step {ctx.loop.local_steps}")
+            sys.stdout.flush()
+            os._exit(self.EXIT_CODE)
+
+
 class StepCounterHook(Hook):
     """``global_step/sec`` every ``every_n_steps`` global steps into the event file of ``train_dir`` itself — the default
     ``StepCounterHook`` that ``MonitoredTrainingSession`` installs on the chief.  ``images/sec`` is

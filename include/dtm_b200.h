@@ -240,6 +240,10 @@ void dtm_loader_destroy(void* loader);
 
 /* ---- peer-memory communication (replaces the reference's gRPC parameter-server traffic: main.py:58-60, :80-93;
  *      mnist_input.py:262-267) ------------------------------------------------------------------------------------ */
+/* Cycle budget of the cross-GPU spin-waits on the current device (default 2.4e11, about two minutes: ranks may reach a
+ * collective seconds apart).  A wait that exceeds it prints "[dtm watchdog] peer barrier (a rank did not arrive)" and
+ * traps - the kernel-level counterpart of the reference's session failing when a worker disappears (main.py:140-146). */
+int dtm_set_comm_watchdog(long long cycles);
 /* Symmetric memory: cudaMalloc + zero-fill + CUDA IPC handle (64 bytes, host memory) to be exchanged between the
  * ranks of one node; dtm_symm_open maps a peer's allocation into this process. */
 int dtm_symm_alloc(size_t bytes, void** ptr, unsigned char* handle64);

@@ -51,6 +51,8 @@ flags.DEFINE_boolean("use_test_split", False, "Train on the test split, as the r
 flags.DEFINE_string("engine", "auto", "auto | native (sm_100a kernels) | torch (portable oracle path)")
 flags.DEFINE_string("backend", "", "torch.distributed backend for the control plane ('' = nccl on GPU, gloo on CPU)")
 flags.DEFINE_integer("num_gpus", 0, "Tower mode: spawn one worker process per GPU on this node (0 = off)")
+flags.DEFINE_integer("max_restarts", 0, "Supervised run: restart the worker set from the newest checkpoint up to this many times "
+                                        "when a worker fails (the recoverable session of MonitoredTrainingSession)")
 flags.DEFINE_boolean("verbose_steps", False, 'Print "training" and the step every iteration like the reference (main.py:149-150)')
 flags.DEFINE_float("save_checkpoint_secs", -1.0, "Seconds between checkpoints (-1 = parameter manager, default 600)")
 flags.DEFINE_integer("seed", -1, "Random seed (-1 = parameter manager)")
@@ -187,6 +189,8 @@ def train():
     feeder = DeviceFeeder(engine, source) if use_cuda else None
 
     hooks = [trainer.StopAtStepHook(last_step=max_steps), trainer.NanLossHook()]
+    if os.environ.get("DTM_FAULT_INJECT"):
+        hooks.append(trainer.FaultInjectionHook(os.environ["DTM_FAULT_INJECT"], role.rank, int(os.environ.get("DTM_RESTART_COUNT", "0"))))
     saver = None
     if getattr(engine, "sharded", False):   # every rank helps assembling checkpoints; only the chief writes them
         saver = checkpointing.CheckpointSaver(FLAGS.train_dir, spec, opt.kind, save_secs=hp.save_checkpoint_secs,
@@ -251,10 +255,20 @@ def train():
 
 
 def main(argv=None):
-    if FLAGS.num_gpus and FLAGS.num_gpus > 1 and not FLAGS.worker_hosts:
+    supervised = os.environ.get("DTM_SUPERVISED") == "1"
+    towers = FLAGS.num_gpus and FLAGS.num_gpus > 1 and not FLAGS.worker_hosts
+    if not supervised and (towers or (FLAGS.max_restarts > 0 and not FLAGS.worker_hosts)):
         from distributed_tensorflow_ibm_mnist_b200.parallel.towers import launch_towers
 
-        return launch_towers(FLAGS.num_gpus, [a for a in sys.argv[1:] if not a.startswith("--num_gpus")], script=os.path.abspath(__file__))
+        args, skip = [], False
+        for a in sys.argv[1:]:       # the supervisor's own flags stay here ("--flag=v" and "--flag v" spellings)
+            if skip:
+                skip = False
+            elif a.split("=", 1)[0] in ("--num_gpus", "--max_restarts"):
+                skip = "=" not in a
+            else:
+                args.append(a)
+        return launch_towers(FLAGS.num_gpus if towers else 1, args, script=os.path.abspath(__file__), max_restarts=FLAGS.max_restarts)
     return train()
 
 

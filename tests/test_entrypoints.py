@@ -176,3 +176,29 @@ def test_tower_mode_spawns_one_worker_per_device(tmp_path):
     rd = BundleReader(os.path.join(train_dir, "model.ckpt-6"))
     assert int(rd.get("global_step")) == 6 and rd.get("conv1/weights").shape == (5, 5, 1, 32)
     assert os.path.exists(os.path.join(train_dir, "graph.pbtxt"))
+
+
+def test_supervisor_restarts_failed_worker_set_from_checkpoint(tmp_path):
+    """Recoverable session (reference main.py:140-146 -> _RecoverableSession): worker 1 of a two-tower job
+    dies without clean-up after 4 steps; the supervisor stops the survivor, restarts both, they restore the chief's newest
+    checkpoint and finish the GLOBAL step budget."""
+    train_dir = str(tmp_path / "recover")
+    env = dict(ENV, DTM_FAULT_INJECT="1:4")
+    r = subprocess.run([sys.executable, "main.py", "--num_gpus", "2", "--max_restarts=1", f"--train_dir={train_dir}", "--model=baseline",
+                        "--batch_size=8", "--max_steps=9", "--test_interval=100", "--optimizer=momentum", "--base_lr=0.02",
+                        "--engine=torch", "--save_checkpoint_secs=0"], cwd=ROOT, env=env, capture_output=True, text=True, timeout=400)
+    assert r.returncode == 0, (r.stdout[-2500:], r.stderr[-2500:])
+    assert "[fault-injection] worker 1 dies after local step 4" in r.stdout
+    assert "[supervisor] worker 1 exited with status 43; restarting all 2 worker(s) from the newest checkpoint (restart 1 of 1)" in r.stdout
+    import re
+
+    m = re.search(r"restored checkpoint at global step (\d+)", r.stdout)
+    assert m and 1 <= int(m.group(1)) <= 5, r.stdout[-2000:]
+    from distributed_tensorflow_ibm_mnist_b200.formats.tensor_bundle import BundleReader
+
+    assert int(BundleReader(os.path.join(train_dir, "model.ckpt-9")).get("global_step")) == 9
+    # without restarts left the failure is the job's result
+    r = subprocess.run([sys.executable, "main.py", "--num_gpus=2", f"--train_dir={tmp_path / 'norestart'}", "--model=baseline",
+                        "--batch_size=8", "--max_steps=9", "--engine=torch", "--save_checkpoint_secs=-1"], cwd=ROOT,
+                       env=dict(ENV, DTM_FAULT_INJECT="0:2"), capture_output=True, text=True, timeout=400)
+    assert r.returncode == 43 and "no restarts left" in r.stdout

@@ -28,8 +28,19 @@ def main() -> int:
 
     spec = presets.make_spec(args.preset)
     B = args.batch
-    eng = NativeEngine(spec, B, optimizer="adam", use_graph=True)
+    world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    comm = None
+    if world > 1:       # under torchrun: the multi-GPU step (rank 0 reports its own device's timeline)
+        import torch.distributed as dist
+        from distributed_tensorflow_ibm_mnist_b200.parallel.peer_comm import PeerComm
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        comm = PeerComm(dist.group.WORLD, torch.device("cuda", local))
+    eng = NativeEngine(spec, B, optimizer="adam", use_graph=True, comm=comm, device=torch.device("cuda", local))
     eng.load_params(oracle.init_params(spec))
+    if comm is not None:
+        eng.broadcast_params()
     x = torch.randint(0, 256, (B, spec.image_pixels), dtype=torch.uint8).cuda()
     y = torch.randint(0, 10, (B,), dtype=torch.int32).cuda()
     eng.stage_batch(0, x, y)
@@ -40,6 +51,10 @@ def main() -> int:
         for _ in range(args.steps):
             eng.train_step(0)
         torch.cuda.synchronize()
+    if rank != 0:
+        torch.cuda.synchronize()
+        dist.barrier()
+        return 0
     evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA and "Memcpy" not in e.name and "Memset" not in e.name]
     recs = sorted(({"name": e.name, "start_us": e.time_range.start, "dur_us": e.time_range.end - e.time_range.start} for e in evs),
                   key=lambda r: r["start_us"])
@@ -64,6 +79,8 @@ def main() -> int:
         print(f"  +{r['start_us'] - t0:7.1f} us  dur {r['dur_us']:6.1f}  {'gap %5.1f' % gap if gap > 0.2 else 'overlap  ' if gap < -0.2 else '         '}  {name}")
         busy_end = max(busy_end, r["start_us"] + r["dur_us"])
     print(f"  end of last kernel +{busy_end - t0:.1f} us ; idle before the next step's first kernel {recs[b]['start_us'] - busy_end:.1f} us")
+    if world > 1:
+        dist.barrier()
     return 0
 
 
