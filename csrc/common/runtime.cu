@@ -76,7 +76,7 @@ int device_sm_count() {
 // 0 = off, 1 = strict (a kernel reads nothing from global memory before its dependency wait), 2 = early weights (kernels
 // may stage WEIGHTS before the wait; only valid when the caller knows that no weight is written by the kernel launched
 // immediately before - true for the training engine's schedule, which opts in around its own launches).
-static int g_pdl_mode = -1;
+static thread_local int g_pdl_mode = -1;   // per host thread: the towers of a single-process job set it around their own launches
 int pdl_mode() {
   if (g_pdl_mode >= 0) return g_pdl_mode;
   const char* e = getenv("DTM_PDL");   // read per launch: a graph capture bakes the choice in, tools can A/B in one process

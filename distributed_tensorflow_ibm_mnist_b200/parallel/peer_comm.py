@@ -16,10 +16,10 @@ import os
 from ctypes import c_int, c_size_t, c_void_p
 
 import torch
-import torch.distributed as dist
 
 from ..ops import _lib
 from ..ops._lib import check, current_stream, ptr
+from .control_plane import as_plane
 
 MAX_RANKS = 8
 P, I = c_void_p, c_int
@@ -31,6 +31,18 @@ _lib.register("dtm_fused_allreduce_update", [P, P, P, I, I, P, P, P, P, P, I, I,
 _lib.register("dtm_allreduce_f32", [P, P, P, I, I, P, I, P, P])
 _lib.register("dtm_broadcast_f32", [P, P, I, I, I, P, P])
 _lib.register("dtm_set_comm_watchdog", [ctypes.c_longlong])
+ULL = ctypes.c_ulonglong
+_lib.register("dtm_vmm_supported", [I, P, P, P])
+_lib.register("dtm_vmm_create", [c_size_t, I, P, P])
+_lib.register("dtm_vmm_export_fd", [ULL, P])
+_lib.register("dtm_vmm_import_fd", [I, P])
+_lib.register("dtm_vmm_map", [ULL, c_size_t, I, P])
+_lib.register("dtm_vmm_grant", [P, c_size_t, I])
+_lib.register("dtm_vmm_unmap", [P, c_size_t])
+_lib.register("dtm_vmm_release", [ULL])
+_lib.register("dtm_mc_create", [I, c_size_t, P])
+_lib.register("dtm_mc_add_device", [ULL, I])
+_lib.register("dtm_mc_bind", [ULL, ULL, c_size_t])
 
 
 class PeerCtx(ctypes.Structure):
@@ -59,11 +71,79 @@ class SymmetricBuffer:
         self._opened: list[int] = []
         self.base = 0
         self._symm = None
-        if comm.nvls:
+        self._vmm: dict | None = None
+        if comm.allocator == "own":
+            self._init_own()
+        elif comm.allocator == "torch":
             self._init_multicast()
         else:
             self._init_ipc()
         self.ptrs_dev = torch.tensor(self.ptrs, dtype=torch.int64, device=comm.device)   # float* const* for the kernels
+
+    def _init_own(self) -> None:
+        """Our own allocator (csrc/comm/symm_vmm.cu): cuMemCreate + peer mappings + multicast object.  Between processes the
+        allocation and multicast handles travel as file descriptors over unix sockets; threads of one process share them
+        directly."""
+        lib, comm, plane = _lib.load(), self.comm, self.comm.plane
+        dev = comm.device.index
+        gran = comm.vmm_granularity
+        nbytes = (self.nbytes + gran - 1) // gran * gran
+        h, va = ULL(0), c_void_p()
+        check(lib.dtm_vmm_create(nbytes, dev, ctypes.byref(h), ctypes.byref(va)), "vmm_create")
+        mine = {"handle": h.value, "va": va.value, "bytes": nbytes, "maps": [], "imported": [], "mc": None}
+
+        def share(handles: list[int]) -> list[list[int]]:
+            """Per rank: that rank's handles, usable in this process."""
+            if plane.same_process:
+                return plane.all_gather_object(list(handles))
+            fds = []
+            for hv in handles:
+                fd = c_int(-1)
+                check(lib.dtm_vmm_export_fd(ULL(hv), ctypes.byref(fd)), "vmm_export_fd")
+                fds.append(fd.value)
+            got = plane.exchange_fds(fds)
+            out = []
+            for j, lst in enumerate(got):
+                if j == comm.rank:
+                    out.append(list(handles))
+                else:
+                    hs = []
+                    for fd in lst:
+                        ih = ULL(0)
+                        check(lib.dtm_vmm_import_fd(fd, ctypes.byref(ih)), f"vmm_import_fd(rank {j})")
+                        os.close(fd)
+                        hs.append(ih.value)
+                        mine["imported"].append(ih.value)
+                    out.append(hs)
+            for fd in fds:
+                os.close(fd)
+            return out
+
+        peers = share([h.value])
+        self.ptrs = []
+        for j in range(comm.world_size):
+            if j == comm.rank:
+                self.ptrs.append(va.value)
+                continue
+            pva = c_void_p()
+            check(lib.dtm_vmm_map(ULL(peers[j][0]), nbytes, dev, ctypes.byref(pva)), f"vmm_map(rank {j})")
+            self.ptrs.append(pva.value)
+            mine["maps"].append(pva.value)
+        if comm.nvls:
+            mc = ULL(0)
+            if comm.rank == 0:
+                check(lib.dtm_mc_create(comm.world_size, nbytes, ctypes.byref(mc)), "mc_create")
+            mc_h = share([mc.value] if comm.rank == 0 else [])[0][0]
+            check(lib.dtm_mc_add_device(ULL(mc_h), dev), "mc_add_device")
+            plane.barrier()                                  # every device is part of the object before anybody binds
+            check(lib.dtm_mc_bind(ULL(mc_h), h, nbytes), "mc_bind")
+            plane.barrier()
+            mva = c_void_p()
+            check(lib.dtm_vmm_map(ULL(mc_h), nbytes, dev, ctypes.byref(mva)), "vmm_map(multicast)")
+            self.mc_ptr = mva.value
+            mine["mc"] = (mc_h, mva.value)
+        self._vmm = mine
+        self.local_u8 = torch.as_tensor(_CudaBuffer(va.value, self.nbytes), device=comm.device)
 
     def _init_ipc(self) -> None:
         lib, comm = _lib.load(), self.comm
@@ -71,8 +151,10 @@ class SymmetricBuffer:
         handle = (ctypes.c_ubyte * 64)()
         check(lib.dtm_symm_alloc(self.nbytes, ctypes.byref(base), handle), "symm_alloc")
         self.base = base.value
-        handles: list = [None] * comm.world_size
-        dist.all_gather_object(handles, bytes(handle), group=comm.group)
+        if comm.plane.same_process:
+            raise RuntimeError("CUDA IPC handles cannot be opened by the process that created them; single-process tower mode "
+                               "needs the VMM allocator (DTM_SYMM=own)")
+        handles = comm.plane.all_gather_object(bytes(handle))
         self.ptrs: list[int] = []
         for j, h in enumerate(handles):
             if j == comm.rank:
@@ -91,7 +173,7 @@ class SymmetricBuffer:
         import torch.distributed._symmetric_memory as symm
         comm = self.comm
         t = symm.empty(self.nbytes, dtype=torch.uint8, device=comm.device)
-        h = symm.rendezvous(t, comm.group)
+        h = symm.rendezvous(t, comm.plane.group)
         ptrs = [int(p) for p in h.buffer_ptrs]
         mc = int(getattr(h, "multicast_ptr", 0) or 0)
         if len(ptrs) != comm.world_size or ptrs[comm.rank] != t.data_ptr() or mc == 0:
@@ -107,6 +189,20 @@ class SymmetricBuffer:
 
     def close(self) -> None:
         lib = _lib.load()
+        if self._vmm is not None:
+            v, self._vmm = self._vmm, None
+            self.local_u8 = None
+            if v["mc"]:
+                lib.dtm_vmm_unmap(c_void_p(v["mc"][1]), v["bytes"])
+                if not self.comm.plane.same_process or self.comm.rank == 0:    # threads share ONE handle to the object
+                    lib.dtm_vmm_release(ULL(v["mc"][0]))
+            for pva in v["maps"]:
+                lib.dtm_vmm_unmap(c_void_p(pva), v["bytes"])
+            if not self.comm.plane.same_process:
+                for ih in v["imported"]:
+                    lib.dtm_vmm_release(ULL(ih))
+            lib.dtm_vmm_unmap(c_void_p(v["va"]), v["bytes"])
+            lib.dtm_vmm_release(ULL(v["handle"]))
         for p in self._opened:
             lib.dtm_symm_close(c_void_p(p))
         self._opened = []
@@ -117,32 +213,58 @@ class SymmetricBuffer:
         self._symm = None
 
 
-def _nvls_available(group, device) -> bool:
-    """Collective decision: can every rank map a multicast buffer?  ``DTM_NVLS=0`` forces the P2P kernels."""
-    mode = os.environ.get("DTM_NVLS", "auto").lower()
-    if mode in ("0", "off", "false", "no"):
-        return False
-    ok = 1
+def _choose_allocator(plane, device) -> tuple[str, bool, int]:
+    """Collective decision -> (allocator, nvls, granularity).
+
+    ``DTM_SYMM`` = ``own`` (csrc/comm/symm_vmm.cu: cuMemCreate + cuMulticast*, the default where the driver offers it) |
+    ``torch`` (torch's symmetric-memory rendezvous, multi-process only) | ``ipc`` (cudaMalloc + CUDA IPC, no multicast) |
+    ``auto``.  ``DTM_NVLS=0`` forces the peer load/store kernels, ``DTM_NVLS=1`` insists on multicast."""
+    lib = _lib.load()
+    want = os.environ.get("DTM_SYMM", "auto").lower()
+    nv = os.environ.get("DTM_NVLS", "auto").lower()
+    nv_off, nv_force = nv in ("0", "off", "false", "no"), nv in ("1", "on", "true", "yes", "force")
+    vmm, mc, gran = c_int(0), c_int(0), c_size_t(0)
     try:
-        import torch.distributed._symmetric_memory as symm
-        t = symm.empty(4096, dtype=torch.uint8, device=device)
-        h = symm.rendezvous(t, group)
-        if not int(getattr(h, "multicast_ptr", 0) or 0):
+        check(lib.dtm_vmm_supported(device.index, ctypes.byref(vmm), ctypes.byref(mc), ctypes.byref(gran)), "vmm_supported")
+    except _lib.NativeError:
+        vmm.value = mc.value = 0
+    own_ok = plane.all_true(bool(vmm.value) and gran.value > 0)
+    own_mc = plane.all_true(bool(mc.value))
+    if want in ("own", "auto") and own_ok:
+        nvls = own_mc and not nv_off
+        if nv_force and not nvls:
+            raise RuntimeError("DTM_NVLS=1 but the devices do not support multicast objects")
+        return "own", nvls, int(gran.value)
+    if want == "own":
+        raise RuntimeError("DTM_SYMM=own but the virtual-memory-management API is not available on every rank")
+    if plane.same_process:
+        raise RuntimeError("single-process tower mode needs the VMM allocator, which this driver/device does not offer")
+    if want in ("torch", "auto") and not nv_off:
+        ok = 1
+        try:
+            import torch.distributed._symmetric_memory as symm
+            t = symm.empty(4096, dtype=torch.uint8, device=device)
+            h = symm.rendezvous(t, plane.group)
+            if not int(getattr(h, "multicast_ptr", 0) or 0):
+                ok = 0
+        except Exception:  # noqa: BLE001 - any failure means "use the IPC path"
             ok = 0
-    except Exception:  # noqa: BLE001 - any failure means "use the IPC path"
-        ok = 0
-    flag = torch.tensor([ok], dtype=torch.int32, device=device)
-    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
-    avail = bool(flag.item())
-    if not avail and mode in ("1", "on", "true", "yes", "force"):
-        raise RuntimeError("DTM_NVLS=1 but NVLS multicast memory is not available on every rank")
-    return avail
+        if plane.all_true(bool(ok)):
+            return "torch", True, 0
+        if want == "torch" or nv_force:
+            raise RuntimeError("torch symmetric memory with a multicast mapping is not available on every rank")
+    return "ipc", False, 0
 
 
 class PeerComm:
     def __init__(self, group, device, *, overlap_ctas: int | None = None):
-        self.group, self.device = group, torch.device(device)
-        self.rank, self.world_size = dist.get_rank(group), dist.get_world_size(group)
+        """``group``: a ``torch.distributed`` process group (ranks are processes) or a control plane
+        (:mod:`.control_plane`; ``ThreadPlane`` = ranks are threads of this process)."""
+        self.plane = as_plane(group)
+        self.group, self.device = getattr(self.plane, "group", None), torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.rank, self.world_size = self.plane.rank, self.plane.world_size
         if self.world_size > MAX_RANKS:
             raise ValueError(f"PeerComm supports up to {MAX_RANKS} ranks on one NVSwitch node")
         torch.cuda.set_device(self.device)
@@ -152,7 +274,8 @@ class PeerComm:
         if ms:
             khz = torch.cuda.get_device_properties(self.device).clock_rate if hasattr(torch.cuda.get_device_properties(self.device), "clock_rate") else 1_965_000
             check(_lib.load().dtm_set_comm_watchdog(int(float(ms) * khz)), "set_comm_watchdog")
-        self.nvls = _nvls_available(group, self.device)   # in-switch reduction + multicast stores (multimem.*)
+        # allocator of the symmetric buffers and transport: in-switch reduction + multicast stores (multimem.*) or peer loads
+        self.allocator, self.nvls, self.vmm_granularity = _choose_allocator(self.plane, self.device)
         # grid cap of a fused exchange that overlaps compute kernels.  NVLS kernel: 0 = one small CTA on every SM, co-resident
         # with the conv backward (2 GPUs: 222 -> 189 us per step against a 64-CTA cap); P2P kernel (512 threads, cannot
         # share an SM with conv2_dgrad): 64 CTAs.
@@ -210,7 +333,7 @@ class PeerComm:
             if self.w_buf is None or self.grad_buf is None or self.bf16_buf is None:
                 raise RuntimeError("PeerComm: FlatParams must be created with comm.flat_allocator() first")
             self.ctx = self._make_ctx(self.grad_buf, self.w_buf, self.bf16_buf)
-            dist.barrier(group=self.group)   # every rank has mapped every buffer before the first kernel touches a peer
+            self.plane.barrier()   # every rank has mapped every buffer before the first kernel touches a peer
         return self.ctx
 
     # ---- hot path ------------------------------------------------------------------------------------
@@ -248,7 +371,7 @@ class PeerComm:
         if self._scratch is None or self._scratch.nbytes < nbytes:
             self._scratch = self._alloc(max(nbytes, 1 << 20))
             self._scratch_ctx = self._make_ctx(None, None)
-            dist.barrier(group=self.group)
+            self.plane.barrier()
         return self._scratch
 
     def all_reduce(self, x: torch.Tensor, mode: str = "auto", nvls: bool | None = None) -> torch.Tensor:
@@ -289,12 +412,11 @@ class PeerComm:
             for r in range(self.world_size):
                 a, b = self.shard_range(lo, hi, r)
                 if b > a:
-                    dist.broadcast(out[a:b], src=dist.get_global_rank(self.group, r) if self.group is not dist.group.WORLD else r,
-                                   group=self.group)
+                    self.plane.broadcast_tensor(out[a:b], r)
         return out
 
     def barrier(self) -> None:
-        dist.barrier(group=self.group)
+        self.plane.barrier()
 
     def close(self, collective: bool = True) -> None:
         """Unmap and free the symmetric buffers.  ``collective=False`` skips the rendezvous with the other ranks (error paths:
@@ -302,7 +424,7 @@ class PeerComm:
         torch.cuda.synchronize(self.device)
         if collective:
             try:
-                dist.barrier(group=self.group)
+                self.plane.barrier()
             except Exception:
                 pass
         for b in self._buffers:

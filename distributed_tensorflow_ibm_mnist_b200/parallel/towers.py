@@ -4,8 +4,9 @@ The reference only alludes to towers (comment mnist_input.py:127-130, README lin
 and the ``return_grad`` hook of ``train()``, mnist_input.py:246/:272).  On B200 the idiomatic shape of "k towers with
 averaged gradients" is one process per GPU: each tower runs the full kernel sequence on its own sub-batch and the
 tower gradients are averaged by the fused peer-memory all-reduce+update kernel (parallel/peer_comm.py) — the in-graph
-"average_gradients" of the tower script becomes a single kernel over NVLink.  :func:`launch_towers` spawns the k
-worker processes with a private loopback rendezvous and waits for them.
+"average_gradients" of the tower script becomes a single kernel over NVLink.  Two forms: :func:`run_tower_threads` drives the k
+GPUs from ONE process (one thread + one engine per GPU, ``--num_gpus=k``); :func:`launch_towers` spawns k worker processes
+with a private loopback rendezvous (``--tower_procs``, and the only form on CPU) and supervises them.
 """
 from __future__ import annotations
 
@@ -83,3 +84,39 @@ def launch_towers(num_gpus: int, argv: list[str], *, script: str, max_restarts: 
         attempt += 1
         out(f"[supervisor] worker {failed[0]} exited with status {failed[1]}; restarting all {max(1, num_gpus)} worker(s) from the "
             f"newest checkpoint (restart {attempt} of {max_restarts})")
+
+
+def run_tower_threads(num_gpus: int, worker) -> int:
+    """Single-process tower mode: ``num_gpus`` threads of THIS process, each driving one GPU with its own engine, streams and
+    CUDA graphs; ``worker(role, plane)`` is the ordinary training function.  The towers' gradients meet in the same fused
+    peer-memory kernels as in the multi-process form - the symmetric buffers come from the VMM allocator, every GPU maps its
+    peers' allocations and the multicast object directly (no IPC handles, no sockets, no ports, no torch.distributed).
+    Python's interpreter lock serialises the towers' host code, so the per-step launch work of k towers adds up: with many
+    GPUs the process form (``--tower_procs``) keeps the GPUs busier."""
+    import threading
+    import traceback
+
+    from ..cluster.spec import Role
+    from .control_plane import ThreadPlane
+
+    from ..ops import _lib
+
+    _lib.load()
+    print(f"single-process tower mode: {num_gpus} GPUs driven by pid {os.getpid()}", flush=True)
+    planes = ThreadPlane.make(num_gpus)
+    rcs = [1] * num_gpus
+
+    def run(rank: int) -> None:
+        try:
+            rcs[rank] = int(worker(Role("worker", rank, rank == 0, rank, num_gpus), planes[rank]) or 0)
+        except BaseException:  # noqa: BLE001 - report, then release the siblings that wait for this tower
+            traceback.print_exc()
+            rcs[rank] = 1
+            planes[rank].abort()
+
+    threads = [threading.Thread(target=run, args=(r,), name=f"tower-{r}") for r in range(num_gpus)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    return max(rcs)

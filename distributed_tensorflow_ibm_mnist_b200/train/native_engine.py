@@ -428,7 +428,7 @@ class NativeEngine:
             # conv1_wgrad, the early optimizer update) compete for SMs, the block scheduler serves the main chain first
             cap = torch.cuda.Stream(device=self.device, priority=self._main_priority)
             cap.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.graph(g, stream=cap):
+            with torch.cuda.graph(g, stream=cap, capture_error_mode="thread_local"):   # sibling tower threads keep working
                 self._step_body(slot)
             torch.cuda.current_stream().wait_stream(cap)
             self._restore(snap)

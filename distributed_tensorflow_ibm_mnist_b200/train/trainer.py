@@ -182,7 +182,8 @@ class MonitoredTrainingLoop:
         self._t0 = None
         # A sharded engine (fused multi-GPU update) needs every rank to take part in assembling a checkpoint, so the
         # chief's time-based decision is broadcast at fixed step intervals and all ranks act on it together.
-        self.group = group
+        self.group = group        # torch.distributed process group or a control plane (parallel/control_plane.py)
+        self._cp = None
         self.collective_saves = bool(getattr(engine, "sharded", False)) and group is not None and saver is not None
         self.save_poll_every = max(1, save_poll_every)
 
@@ -223,26 +224,23 @@ class MonitoredTrainingLoop:
         if self.log_every and self.local_steps % self.log_every == 0:
             self.out("%d steps executed on worker %d." % (self.local_steps, self.task_id))
 
+    def _plane(self):
+        if self._cp is None and self.group is not None:
+            from ..parallel.control_plane import as_plane
+
+            self._cp = as_plane(self.group)
+        return self._cp
+
     def any_rank(self, flag: bool) -> bool:
         """True on every rank as soon as ``flag`` is true on one of them (collective; a no-op without a group)."""
-        if self.group is None:
+        cp = self._plane()
+        if cp is None or cp.world_size <= 1:
             return bool(flag)
-        import torch.distributed as dist
-
-        if dist.get_world_size(self.group) <= 1:
-            return bool(flag)
-        on_gpu = dist.get_backend(self.group) == "nccl"
-        t = torch.tensor([1.0 if flag else 0.0], device=getattr(self.engine, "device", "cpu") if on_gpu else "cpu")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
-        return bool(t.item() > 0.0)
+        return cp.any_true(flag)
 
     def _agree(self, flag: bool) -> bool:
         """The chief's decision, known to every rank."""
-        import torch.distributed as dist
-
-        box = [bool(flag)]
-        dist.broadcast_object_list(box, src=0, group=self.group)
-        return bool(box[0])
+        return bool(self._plane().broadcast_object(bool(flag), 0))
 
     def summary_tensors(self) -> dict:
         eng = self.engine

@@ -250,6 +250,24 @@ int dtm_symm_alloc(size_t bytes, void** ptr, unsigned char* handle64);
 int dtm_symm_open(const unsigned char* handle64, void** peer_ptr);
 int dtm_symm_close(void* peer_ptr);
 int dtm_symm_free(void* ptr);
+/* Symmetric memory on the virtual-memory-management API, with NVLink-SHARP multicast binding (csrc/comm/symm_vmm.cu) - the
+ * communicator's own allocator (SURVEY X-a); dtm_symm_* above is the cudaMalloc + CUDA-IPC fallback, which cannot be bound
+ * to a multicast object.  All sizes are multiples of the granularity dtm_vmm_supported reports.
+ *   create -> export_fd -> (fd travels to the peer process) -> import_fd -> map      peer access between processes
+ *   create -> grant(other device)                                                   peer access inside one process
+ *   mc_create (once, N devices) -> [export/import] -> mc_add_device (every device) -> barrier -> mc_bind (every device, its
+ *   own allocation) -> barrier -> map(mc handle)                                    one address that reaches all N copies */
+int dtm_vmm_supported(int device, int* vmm, int* multicast, size_t* granularity);
+int dtm_vmm_create(size_t bytes, int device, unsigned long long* handle, void** va);
+int dtm_vmm_export_fd(unsigned long long handle, int* fd);
+int dtm_vmm_import_fd(int fd, unsigned long long* handle);
+int dtm_vmm_map(unsigned long long handle, size_t bytes, int device, void** va);
+int dtm_vmm_grant(void* va, size_t bytes, int device);
+int dtm_vmm_unmap(void* va, size_t bytes);
+int dtm_vmm_release(unsigned long long handle);
+int dtm_mc_create(int num_devices, size_t bytes, unsigned long long* mc_handle);
+int dtm_mc_add_device(unsigned long long mc_handle, int device);
+int dtm_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, size_t bytes);
 /* One kernel: cross-GPU barrier, reduce-scatter of grad[lo:hi) over peer loads, scale 1/N + weight decay + optimizer
  * + EMA on this rank's shard, all-gather of the new weights by peer stores (bf16 only for seg_gather_bf16 variables,
  * fp32 otherwise), barrier, local bf16 shadow of the fp32-gathered variables + gradient clearing; with do_finish the

@@ -50,7 +50,9 @@ flags.DEFINE_string("test_data", "", "Comma-separated TFRecord files for the tes
 flags.DEFINE_boolean("use_test_split", False, "Train on the test split, as the reference does (main.py:85)")
 flags.DEFINE_string("engine", "auto", "auto | native (sm_100a kernels) | torch (portable oracle path)")
 flags.DEFINE_string("backend", "", "torch.distributed backend for the control plane ('' = nccl on GPU, gloo on CPU)")
-flags.DEFINE_integer("num_gpus", 0, "Tower mode: spawn one worker process per GPU on this node (0 = off)")
+flags.DEFINE_integer("num_gpus", 0, "Tower mode: k GPUs of this node driven by ONE process, one thread and one engine per GPU "
+                                    "(0 = off); see --tower_procs")
+flags.DEFINE_boolean("tower_procs", False, "Tower mode with one worker PROCESS per GPU (the only form for --engine=torch)")
 flags.DEFINE_integer("max_restarts", 0, "Supervised run: restart the worker set from the newest checkpoint up to this many times "
                                         "when a worker fails (the recoverable session of MonitoredTrainingSession)")
 flags.DEFINE_boolean("verbose_steps", False, 'Print "training" and the step every iteration like the reference (main.py:149-150)')
@@ -106,7 +108,9 @@ def setup_distribute():
     return cluster, role
 
 
-def train():
+def train(role=None, plane=None, hp=None):
+    """One worker.  ``role``/``plane`` are given by the single-process tower mode (the worker is a thread, its control plane a
+    ThreadPlane); otherwise the role comes from the flags and the control plane is a torch.distributed process group."""
     import torch
 
     from distributed_tensorflow_ibm_mnist_b200.cluster import spec as cluster_spec
@@ -115,10 +119,15 @@ def train():
     from distributed_tensorflow_ibm_mnist_b200.models import oracle, presets
     from distributed_tensorflow_ibm_mnist_b200.train import checkpointing, monitor as monitor_cb, trainer
 
-    hp = _configure_hyper_params()
-    cluster, role = setup_distribute()
-    if role is None:
-        return 0  # parameter-server process: done
+    threaded = plane is not None
+    if hp is None:
+        hp = _configure_hyper_params()
+    if threaded:
+        cluster = cluster_spec.ClusterSpec()
+    else:
+        cluster, role = setup_distribute()
+        if role is None:
+            return 0  # parameter-server process: done
     is_chief = role.is_chief
     max_steps, test_interval, batch_size = (tf_parameter_mgr.getMaxSteps(), tf_parameter_mgr.getTestInterval(),
                                             tf_parameter_mgr.getTrainBatchSize())
@@ -126,13 +135,18 @@ def train():
     use_cuda = torch.cuda.is_available() and FLAGS.engine != "torch"
     if FLAGS.engine == "native" and not torch.cuda.is_available():
         raise SystemExit("--engine=native needs a CUDA device")
-    local_rank = int(os.environ.get("LOCAL_RANK", role.rank % max(1, torch.cuda.device_count()) if use_cuda else 0))
+    local_rank = role.rank if threaded else int(os.environ.get("LOCAL_RANK", role.rank % max(1, torch.cuda.device_count()) if use_cuda else 0))
     device = torch.device("cuda", local_rank) if use_cuda else torch.device("cpu")
     if use_cuda:
         torch.cuda.set_device(device)
 
     group = store = comm = None
-    if role.world_size > 1:
+    if threaded:
+        from distributed_tensorflow_ibm_mnist_b200.parallel.peer_comm import PeerComm
+
+        group = plane
+        comm = PeerComm(plane, device)
+    elif role.world_size > 1:
         backend = FLAGS.backend or ("nccl" if use_cuda else "gloo")
         group, store = cluster_spec.init_worker_group(cluster, role, backend)
         if use_cuda:
@@ -238,7 +252,10 @@ def train():
     m = engine.metrics()
     print("final: global_step=%d loss=%.4f accuracy=%.3f" % (m["global_step"], m["total_loss"], m["accuracy"]))
 
-    if group is not None:
+    if threaded:
+        plane.barrier()
+        comm.close()
+    elif group is not None:
         import torch.distributed as dist
 
         cluster_spec.signal_worker_done(store)
@@ -254,21 +271,39 @@ def train():
     return 0
 
 
-def main(argv=None):
-    supervised = os.environ.get("DTM_SUPERVISED") == "1"
-    towers = FLAGS.num_gpus and FLAGS.num_gpus > 1 and not FLAGS.worker_hosts
-    if not supervised and (towers or (FLAGS.max_restarts > 0 and not FLAGS.worker_hosts)):
-        from distributed_tensorflow_ibm_mnist_b200.parallel.towers import launch_towers
+def _strip(argv, names):
+    """argv without the given flags ("--flag=v" and "--flag v" spellings)."""
+    out, skip = [], False
+    for a in argv:
+        if skip:
+            skip = False
+        elif a.split("=", 1)[0] in names:
+            skip = "=" not in a and a.split("=", 1)[0] not in ("--tower_procs",)
+        else:
+            out.append(a)
+    return out
 
-        args, skip = [], False
-        for a in sys.argv[1:]:       # the supervisor's own flags stay here ("--flag=v" and "--flag v" spellings)
-            if skip:
-                skip = False
-            elif a.split("=", 1)[0] in ("--num_gpus", "--max_restarts"):
-                skip = "=" not in a
-            else:
-                args.append(a)
-        return launch_towers(FLAGS.num_gpus if towers else 1, args, script=os.path.abspath(__file__), max_restarts=FLAGS.max_restarts)
+
+def main(argv=None):
+    from distributed_tensorflow_ibm_mnist_b200.parallel import towers
+
+    supervised = os.environ.get("DTM_SUPERVISED") == "1"
+    k = FLAGS.num_gpus if (FLAGS.num_gpus and FLAGS.num_gpus > 1 and not FLAGS.worker_hosts) else 0
+    use_threads = False
+    if k and not FLAGS.tower_procs and FLAGS.engine != "torch":
+        import torch
+
+        use_threads = torch.cuda.is_available() and torch.cuda.device_count() >= k
+    me = os.path.abspath(__file__)
+    if not supervised:
+        if k and not use_threads:       # one worker process per device
+            return towers.launch_towers(k, _strip(sys.argv[1:], ("--num_gpus", "--max_restarts", "--tower_procs")), script=me,
+                                        max_restarts=FLAGS.max_restarts)
+        if FLAGS.max_restarts > 0 and not FLAGS.worker_hosts:      # one supervised process (which may itself drive k GPUs)
+            return towers.launch_towers(1, _strip(sys.argv[1:], ("--max_restarts",)), script=me, max_restarts=FLAGS.max_restarts)
+    if use_threads:
+        hp = _configure_hyper_params()
+        return towers.run_tower_threads(k, lambda role, plane: train(role, plane, hp))
     return train()
 
 
