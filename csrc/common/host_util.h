@@ -30,6 +30,7 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64
                       uint32_t box_inner, uint32_t box_outer, uint32_t swizzle_bytes);
 
 int device_sm_count();
+int device_slot();   // current device index clamped to [0, 64): index of per-device one-time set-up flags
 
 // Access-policy window the optimizer update kernels are launched with (dtm_set_update_l2_window); null when off.
 struct L2Window {

@@ -61,6 +61,12 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64
   return 0;
 }
 
+int device_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) return 0;
+  return dev < 64 ? dev : 63;
+}
+
 int device_sm_count() {
   static int cached[64];
   int dev = 0;

@@ -265,13 +265,14 @@ extern "C" int dtm_conv1_fwd(const void* x, int in_is_float, int channels, const
   uint8_t* p = static_cast<uint8_t*>(p1_planes);
   uint8_t* a = static_cast<uint8_t*>(argmax);
   __nv_bfloat16* r = static_cast<__nv_bfloat16*>(pool_raw);
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {};     // per device: function attributes belong to a device's context
+  const int dev_slot = device_slot();
+  if (!configured[dev_slot]) {
     DTM_CUDA_OK(cudaFuncSetAttribute(conv1_tc_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, T1Geom<1>::SMEM));
     DTM_CUDA_OK(cudaFuncSetAttribute(conv1_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, T1Geom<1>::SMEM));
     DTM_CUDA_OK(cudaFuncSetAttribute(conv1_tc_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, T1Geom<3>::SMEM));
     DTM_CUDA_OK(cudaFuncSetAttribute(conv1_tc_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, T1Geom<3>::SMEM));
-    configured = true;
+    configured[dev_slot] = true;
   }
   // persistent CTAs; the 1-channel geometry needs ~43 KiB of shared memory, so two CTAs share an SM and overlap their phases
   const int per_sm = channels == 1 ? 2 : 1;

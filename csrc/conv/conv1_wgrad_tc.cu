@@ -232,11 +232,12 @@ extern "C" int dtm_conv1_wgrad_tc(const void* x, int in_is_float, int channels, 
   if (channels != 1 && channels != 3) return dtm_fail("conv1_wgrad: channels must be 1 or 3");
   if (batch <= 0) return dtm_fail("conv1_wgrad: batch must be positive");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {};     // per device: function attributes belong to a device's context
+  const int dev_slot = device_slot();
+  if (!configured[dev_slot]) {
     DTM_CUDA_OK(cudaFuncSetAttribute(conv1_wgrad_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, W1Geom<1>::SMEM));
     DTM_CUDA_OK(cudaFuncSetAttribute(conv1_wgrad_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, W1Geom<3>::SMEM));
-    configured = true;
+    configured[dev_slot] = true;
   }
   // persistent CTAs (one accumulator and one epilogue each); two per SM overlap staging with MMA issue
   const int grid = min(batch, 2 * device_sm_count());

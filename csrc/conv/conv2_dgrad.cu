@@ -225,11 +225,12 @@ extern "C" int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, cons
   if (lrn && !pool_raw) return dtm_fail("conv2_dgrad: LRN backward needs pool_raw");
   if (!lrn && !p1_planes) return dtm_fail("conv2_dgrad: needs the conv1 activation for the ReLU mask");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {};     // per device: function attributes belong to a device's context
+  const int dev_slot = device_slot();
+  if (!configured[dev_slot]) {
     DTM_CUDA_OK(cudaFuncSetAttribute(conv2_dgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
     DTM_CUDA_OK(cudaFuncSetAttribute(conv2_dgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
-    configured = true;
+    configured[dev_slot] = true;
   }
   const int grid = min(2 * batch, device_sm_count());
   auto launch = [&](auto kern) -> int {

@@ -250,11 +250,12 @@ extern "C" int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const v
   if (lrn && !act2) return dtm_fail("conv2_fwd: LRN needs the act2 buffer");
   if (!w2_bf16 && !packed) return dtm_fail("conv2_fwd: needs weights (w2_bf16 or packed)");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {};     // per device: function attributes belong to a device's context
+  const int dev_slot = device_slot();
+  if (!configured[dev_slot]) {
     DTM_CUDA_OK(cudaFuncSetAttribute(conv2_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C2_SMEM));
     DTM_CUDA_OK(cudaFuncSetAttribute(conv2_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C2_SMEM));
-    configured = true;
+    configured[dev_slot] = true;
   }
   const int grid = min(2 * batch, device_sm_count());
   auto args = [&](auto kern) -> int {

@@ -145,10 +145,11 @@ extern "C" int dtm_conv2_wgrad(const void* p1_planes, const void* dz2_planes, in
   using namespace dtm;
   if (batch <= 0) return dtm_fail("conv2_wgrad: batch must be positive");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {};     // per device: function attributes belong to a device's context
+  const int dev_slot = device_slot();
+  if (!configured[dev_slot]) {
     DTM_CUDA_OK(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
-    configured = true;
+    configured[dev_slot] = true;
   }
   const int gx = min(batch, max(1, device_sm_count() / 2));
   DTM_CUDA_OK(launch_pdl(conv2_wgrad_kernel, dim3(gx, 2), dim3(256), WG_SMEM, s, static_cast<const uint8_t*>(p1_planes),

@@ -317,10 +317,11 @@ extern "C" int dtm_conv_wgrad_fused(const void* p1_planes, const void* dz2_plane
   const char* e = getenv("DTM_FW_NO_CONV1");
   // (values 3 / 5 / 7: conv1 pipeline without its MMAs / without the operand building / without both - timing only)
   const int conv1_on = e ? ((e[0] == '1') ? 0 : atoi(e)) : 1;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {};     // per device: function attributes belong to a device's context
+  const int dev_slot = device_slot();
+  if (!configured[dev_slot]) {
     DTM_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FW_SMEM));
-    configured = true;
+    configured[dev_slot] = true;
   }
   const int gx = min(batch, max(1, device_sm_count() / 2));
   DTM_CUDA_OK(launch_pdl(conv_wgrad_fused_kernel, dim3(gx, 2), dim3(256), FW_SMEM, s, static_cast<const uint8_t*>(p1_planes),

@@ -308,10 +308,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 template <bool A_MN, bool B_MN, int STAGES>
 static int launch_gemm_s(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, dim3 grid, cudaStream_t s) {
   auto kern = gemm_bf16_kernel<A_MN, B_MN, STAGES>;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {};     // per device: function attributes belong to a device's context
+  const int dev_slot = device_slot();
+  if (!configured[dev_slot]) {
     DTM_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes(STAGES)));
-    configured = true;
+    configured[dev_slot] = true;
   }
   DTM_CUDA_OK(launch_pdl_cluster(kern, grid, dim3(256), gemm_smem_bytes(STAGES), s, g.cluster_reduce ? 2 : 1, ta, tb, g));
   DTM_CUDA_OK(cudaGetLastError());

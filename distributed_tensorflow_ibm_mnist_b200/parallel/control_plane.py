@@ -143,7 +143,9 @@ class ThreadPlane:
         return any(self.all_gather_object(bool(flag)))
 
     def broadcast_tensor(self, t: torch.Tensor, src: int) -> None:
-        views = self.all_gather_object(t)
+        # staged through host memory on purpose: a direct cross-device copy makes torch enable peer access for ALL of its
+        # allocations, after which every cudaMalloc / cudaFree synchronises the sibling devices too
+        views = self.all_gather_object(t.cpu() if self.rank == src else None)
         if self.rank != src:
             t.copy_(views[src])
             torch.cuda.synchronize(t.device)

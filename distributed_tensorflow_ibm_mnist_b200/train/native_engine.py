@@ -423,6 +423,14 @@ class NativeEngine:
             self.launches_per_step = self._step_body(slot)
             torch.cuda.synchronize(self.device)
             self._restore(snap)
+            # Towers that are threads of one process go through the capture in lock step: entering a capture empties torch's
+            # allocator cache on EVERY device of the process (cudaFree synchronises those devices), and a sibling that has
+            # already replayed its graph would sit in an exchange kernel waiting for this tower - which then could never
+            # finish its capture.  Both barriers see idle devices.
+            plane = getattr(self.comm, "plane", None)
+            lockstep = plane is not None and plane.same_process
+            if lockstep:
+                plane.barrier()
             g = torch.cuda.CUDAGraph()
             # the critical path (main stream) gets the higher priority: when its kernels and the side-stream kernels (dW3,
             # conv1_wgrad, the early optimizer update) compete for SMs, the block scheduler serves the main chain first
@@ -432,6 +440,8 @@ class NativeEngine:
                 self._step_body(slot)
             torch.cuda.current_stream().wait_stream(cap)
             self._restore(snap)
+            if lockstep:
+                plane.barrier()
             self._graphs[slot] = g
         g.replay()
 

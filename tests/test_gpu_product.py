@@ -27,7 +27,8 @@ import torch
 pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-ENV = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2")
+# a collective that cannot complete should fail these tests in seconds, not after the default two-minute leash
+ENV = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2", DTM_COMM_WATCHDOG_MS=os.environ.get("DTM_COMM_WATCHDOG_MS", "20000"))
 
 
 def _run(args, timeout=600, env=None):
