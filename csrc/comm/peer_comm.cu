@@ -342,6 +342,76 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Replicated one-shot update for SMALL buckets (the conv variables: 52 K elements closing every step).  The fused kernel
+// above pays a chain of dependent latencies at the end of the step - reduce-scatter, all-gather, a second cross-GPU barrier
+// that waits for every remote store - about 30 us for 200 KB.  Here every rank reads ALL peers' gradients itself (N-1 x
+// 200 KB over NVLink, fixed rank order: bit-identical sums everywhere) and applies the whole update to its own copy; the
+// optimizer state of the bucket is replicated.  No all-gather, nothing remote is written, ONE barrier ("the peers' gradients
+// are complete"), and no CTA waits for another CTA, so the launch is an ordinary one.
+//
+// Gradients of this bucket are double-buffered by step parity: a rank may still be reading my buffer of step k when I
+// finish, so step k+1 accumulates into the other buffer, and the buffer of step k is cleared during step k+1 - after that
+// step's barrier, which no peer can pass before it has left step k's kernel.
+__global__ void __launch_bounds__(256, 4)
+replicated_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cfg, dtm_train_state* __restrict__ st, int lo, int hi,
+                         float* const* __restrict__ grad_now, float* __restrict__ grad_prev_local, float* __restrict__ slot0,
+                         float* __restrict__ slot1, float* __restrict__ ema, __nv_bfloat16* __restrict__ w_bf16,
+                         CommCtrl* __restrict__ ctrl, int do_finish) {
+  const int N = ctx.world, r = ctx.rank;
+  pdl_wait();
+  pdl_launch_dependents();
+  const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
+  barrier_ready_publish(ctx, e0 + 1);
+  const UpdateScalars u = make_update_scalars(cfg, st, 1.0f / static_cast<float>(N));
+  float* w_local = ctx.w[r];
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nthreads = gridDim.x * blockDim.x;
+  __shared__ float s_wl[DTM_MAX_SEGMENTS];
+  __shared__ float* s_src[DTM_MAX_RANKS];
+  if (threadIdx.x < DTM_MAX_SEGMENTS) s_wl[threadIdx.x] = 0.0f;
+  if (threadIdx.x < N) s_src[threadIdx.x] = grad_now[threadIdx.x];
+  barrier_ready_wait(ctx, e0 + 1);      // ends with __syncthreads
+  int seg = 0, cur_seg = -1;
+  float cur_sq = 0.0f;
+  for (int i = lo + tid * 4; i < hi; i += nthreads * 4) {
+    const float4 g = reduce_peers(s_src, N, i);
+    seg = segment_advance(cfg, seg, i);
+    const float wd = cfg.seg_wd[seg];
+    const float4 wv = *reinterpret_cast<const float4*>(w_local + i);
+    if (wd != 0.0f) {
+      if (seg != cur_seg) {
+        if (cur_seg >= 0) atomicAdd(&s_wl[cur_seg], cur_sq);
+        cur_seg = seg;
+        cur_sq = 0.0f;
+      }
+      cur_sq += wv.x * wv.x + wv.y * wv.y + wv.z * wv.z + wv.w * wv.w;
+    }
+    const float4 o = update_vec4(cfg, u, wv, g, wd, slot0, slot1, ema, i);
+    *reinterpret_cast<float4*>(w_local + i) = o;
+    *reinterpret_cast<uint2*>(w_bf16 + i) = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+    if (seg == cfg.pack_seg) pack_conv2_vec4(cfg, i - cfg.seg_offset[seg], o);
+    // last step's buffer: every peer has finished with it (see above); the next step accumulates into it again
+    if (grad_prev_local) *reinterpret_cast<float4*>(grad_prev_local + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  if (cur_seg >= 0) atomicAdd(&s_wl[cur_seg], cur_sq);
+  __syncthreads();
+  if (threadIdx.x < cfg.n_segments && s_wl[threadIdx.x] != 0.0f) atomicAdd(&st->wl_sum[threadIdx.x], s_wl[threadIdx.x]);
+  __threadfence();
+  __syncthreads();
+  __shared__ unsigned int s_last;
+  if (threadIdx.x == 0) s_last = (atomicAdd(&ctrl->ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+  __syncthreads();
+  if (s_last) {
+    __threadfence();
+    if (threadIdx.x == 0) {
+      ctrl->ticket = 0;
+      st_release_gpu(&ctrl->epoch, e0 + 2);
+    }
+    if (do_finish) finish_step(cfg, st, u.lr_plain);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Stand-alone all-reduce (sum) of n floats at element offset `off` of the symmetric buffer `buf`.
 //   mode 0 (one-shot): out[i] = sum_j buf_j[i], every rank reads all peers.
 //   mode 1 (two-shot): shard owner reduces and writes the sum back into every rank's buf (in place); out = buf.
@@ -537,6 +607,27 @@ extern "C" int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_upd
   return launch_cooperative(fused_allreduce_update_kernel<false, false>, comm_grid(static_cast<size_t>(hi - lo), max_ctas), 512,
                             static_cast<cudaStream_t>(stream), true, *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
                             static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
+}
+
+extern "C" int dtm_replicated_allreduce_update(const dtm_peer_ctx* ctx, const dtm_update_config* cfg, dtm_train_state* state, int lo,
+                                               int hi, float* const* grad_now_dev, float* grad_prev_local, float* slot0,
+                                               float* slot1, float* ema, void* w_bf16, void* ctrl, int do_finish, void* stream) {
+  using namespace dtm;
+  if (int rc = check_ctx(ctx)) return rc;
+  if (!cfg || !state || !ctrl || !w_bf16 || !grad_now_dev) return dtm_fail("replicated_update: null argument");
+  if (lo < 0 || hi > cfg->total || lo >= hi || lo % 64 || hi % 64) return dtm_fail("replicated_update: bad element range");
+  if (cfg->optimizer == DTM_OPT_ADAM && (!slot0 || !slot1)) return dtm_fail("replicated_update: Adam needs both slots");
+  if (cfg->optimizer == DTM_OPT_MOMENTUM && !slot0) return dtm_fail("replicated_update: Momentum needs slot0");
+  for (int sg = 0; sg < cfg->n_segments; ++sg)
+    if (cfg->seg_gather_bf16[sg] && cfg->seg_offset[sg] < hi && cfg->seg_offset[sg + 1] > lo)
+      return dtm_fail("replicated_update: the range holds a variable whose fp32 master is sharded");
+  const int n4 = (hi - lo) / 4;
+  const int grid = max(1, min((n4 + 255) / 256, device_sm_count()));
+  DTM_CUDA_OK(launch_pdl(replicated_update_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), *ctx, *cfg, state, lo, hi,
+                         grad_now_dev, grad_prev_local, slot0, slot1, ema, static_cast<__nv_bfloat16*>(w_bf16),
+                         static_cast<CommCtrl*>(ctrl), do_finish));
+  DTM_CUDA_OK(cudaGetLastError());
+  return 0;
 }
 
 extern "C" int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, float* mc_buf, int off, int n, float* out, int mode,

@@ -28,6 +28,7 @@ _lib.register("dtm_symm_open", [P, P])
 _lib.register("dtm_symm_close", [P])
 _lib.register("dtm_symm_free", [P])
 _lib.register("dtm_fused_allreduce_update", [P, P, P, I, I, P, P, P, P, P, I, I, P])
+_lib.register("dtm_replicated_allreduce_update", [P, P, P, I, I, P, P, P, P, P, P, P, I, P])
 _lib.register("dtm_allreduce_f32", [P, P, P, I, I, P, I, P, P])
 _lib.register("dtm_broadcast_f32", [P, P, I, I, I, P, P])
 _lib.register("dtm_set_comm_watchdog", [ctypes.c_longlong])
@@ -346,6 +347,21 @@ class PeerComm:
                                                      ptr(flat.slot1), ptr(flat.ema), ptr(flat.w_bf16), ptr(self.ctrl), int(finish),
                                                      self.overlap_ctas if overlapped else 0, current_stream()),
               "fused_allreduce_update")
+
+    def alloc_symmetric(self, nbytes: int) -> SymmetricBuffer:
+        """One more symmetric buffer (collective: every rank, same order)."""
+        b = self._alloc(nbytes)
+        self.plane.barrier()
+        return b
+
+    def replicated_update(self, cfg, state, flat, lo: int, hi: int, grad_now: SymmetricBuffer, grad_prev_local, *, finish: bool = True) -> None:
+        """Small bucket [lo, hi): every rank sums all ranks' gradients out of ``grad_now`` itself and updates its own replica;
+        ``grad_prev_local`` (this rank's buffer of the previous step) is cleared (``dtm_replicated_allreduce_update``)."""
+        ctx = self._ensure_ctx()
+        check(_lib.load().dtm_replicated_allreduce_update(ctypes.byref(ctx), ctypes.byref(cfg), ptr(state), lo, hi, ptr(grad_now.ptrs_dev),
+                                                          ptr(grad_prev_local), ptr(flat.slot0), ptr(flat.slot1), ptr(flat.ema),
+                                                          ptr(flat.w_bf16), ptr(self.ctrl), int(finish), current_stream()),
+              "replicated_update")
 
     def broadcast_params(self, flat, state=None, root: int = 0) -> None:
         """Make the root's weights (and training state scalars) authoritative on every rank."""

@@ -64,7 +64,7 @@ class NativeEngine:
                 self.l2_window = native.set_update_l2_window(self.flat.blob)
             except _lib.NativeError:
                 self.l2_window = None
-        self._graphs: dict[int, torch.cuda.CUDAGraph] = {}
+        self._graphs: dict[tuple, torch.cuda.CUDAGraph] = {}
         self._side = torch.cuda.Stream(device=self.device)
         self._comm_stream = torch.cuda.Stream(device=self.device)
         self._head_stream = torch.cuda.Stream(device=self.device)
@@ -75,6 +75,16 @@ class NativeEngine:
         # stream while the conv backward still runs.
         split = self.flat.offsets["local3/weights"]
         self.buckets = [(split, self.flat.total), (0, split)]
+        # Multi-GPU: the conv bucket closes the step, so its exchange is pure latency.  Default: replicated one-shot update
+        # (every rank sums all ranks' conv gradients itself: one barrier, no all-gather) with the bucket's gradients
+        # double-buffered by step parity; DTM_CONV_EXCHANGE=fused keeps the reduce-scatter / all-gather kernel for it.
+        self._grad_base = None          # summaries: gradients of an extra pass go to a private buffer
+        self._parity = 0
+        self.grad_alt = None
+        self._replicated_conv = self.sharded and os.environ.get("DTM_CONV_EXCHANGE", "replicated") != "fused"
+        if self._replicated_conv:
+            self._grad_alt_buf = comm.alloc_symmetric(split * 4)
+            self.grad_alt = self._grad_alt_buf.view(torch.float32, split)
         self.launches_per_step = 0
         self.trace = None   # set to a list to collect (label, cuda event) marks on the main stream (tools/phase_times.py)
 
@@ -190,6 +200,19 @@ class NativeEngine:
         n = {"sgd": 0, "momentum": 1, "adam": 2}[self.optimizer.lower()]
         return [self._full(self.flat.slot0 if i == 0 else self.flat.slot1) for i in range(n)]
 
+    def _g(self, name: str) -> torch.Tensor:
+        """Where the backward pass accumulates the gradient of ``name``: the flat gradient buffer, the other half of the
+        double-buffered conv bucket on odd steps, or the private buffer of a summary pass."""
+        f = self.flat
+        v, o = self.spec.var(name), f.offsets[name]
+        if self._grad_base is not None:
+            buf = self._grad_base
+        elif self._parity and self.grad_alt is not None and o < self.buckets[1][1]:
+            buf = self.grad_alt
+        else:
+            buf = f.grad
+        return buf[o:o + v.size].view(v.shape)
+
     def gradients(self) -> dict[str, torch.Tensor]:
         return {k: v.cpu() for k, v in self.flat.grad_dict().items()}
 
@@ -267,17 +290,17 @@ class NativeEngine:
         main = torch.cuda.current_stream()
         if self._on("head_bwd") and not self._fuse_dh:
             native.head_backward(h, f.weight("softmax_linear/weights"), self.dlogits, self.dh_last,
-                                 f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
-                                 f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep); n += 1
+                                 self._g("softmax_linear/weights"), self._g("softmax_linear/biases"),
+                                 self._g("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep); n += 1
         elif self._on("head_bwd"):
             self._fork_ev[6].record(main)   # the head's own gradients depend on head_forward only; launched further down
         self._mark("head_bwd")
         if s.fc2:
             # dW4 = h1^T . dY2 ; dY1 = (dY2 . W4^T) * [h1 > 0] ; db3 = colsum(dY1)
-            native.gemm_bf16(self.h1, 1, self.dh_last, 1, f.gradient("local4/weights"), s.fc1, s.fc2, B); n += 1
+            native.gemm_bf16(self.h1, 1, self.dh_last, 1, self._g("local4/weights"), s.fc1, s.fc2, B); n += 1
             native.gemm_bf16(self.dh_last, 0, f.weight_bf16("local4/weights"), 0, self.dh1, B, s.fc1, s.fc2,
                              epilogue=native.EPI_MASK_BF16, ref=self.h1); n += 1
-            native.colsum_bf16(self.dh1, f.gradient("local3/biases")); n += 1
+            native.colsum_bf16(self.dh1, self._g("local3/biases")); n += 1
             dy1 = self.dh1
         else:
             dy1 = self.dh_last
@@ -300,14 +323,14 @@ class NativeEngine:
             self._head_stream.wait_event(self._fork_ev[6])
             with torch.cuda.stream(self._stream(self._head_stream)):
                 native.head_backward(h, f.weight("softmax_linear/weights"), self.dlogits, self.dh_last,
-                                     f.gradient("softmax_linear/weights"), f.gradient("softmax_linear/biases"),
-                                     f.gradient("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep,
+                                     self._g("softmax_linear/weights"), self._g("softmax_linear/biases"),
+                                     self._g("local4/biases" if s.fc2 else "local3/biases"), inv_keep=inv_keep,
                                      dh_ready=True); n += 1
                 self._fork_ev[7].record(self._head_stream)
         self._side.wait_event(self._fork_ev[0])
         with torch.cuda.stream(self._stream(self._side)):
             if self._on("dW3"):
-                native.gemm_bf16(self.p2, 1, dy1, 1, f.gradient("local3/weights"), 3136, s.fc1, B); n += 1
+                native.gemm_bf16(self.p2, 1, dy1, 1, self._g("local3/weights"), 3136, s.fc1, B); n += 1
             self._fork_ev[1].record(self._side)
         self._mark("dP2_gemm")
         if fused_unpool:
@@ -315,7 +338,7 @@ class NativeEngine:
             self._fork_ev[8].record(main)
             self._head_stream.wait_event(self._fork_ev[8])
             with torch.cuda.stream(self._stream(self._head_stream)):
-                native.colsum_bf16(self.dp2.view(B * 49, 64), f.gradient("conv2/biases")); n += 1
+                native.colsum_bf16(self.dp2.view(B * 49, 64), self._g("conv2/biases")); n += 1
                 self._fork_ev[9].record(self._head_stream)
         # bucket 0 (fc + head variables, 98 % of the elements): every gradient is complete once the dW GEMM is done and the
         # last reader of the fc weights (the dP2 GEMM above) has finished -> update it now, on its own stream, beside the
@@ -338,7 +361,7 @@ class NativeEngine:
                 n += 1
                 self._fork_ev[5].record(self._comm_stream)
         if self._on("unpool2") and not fused_unpool:
-            native.unpool2(self.dp2, self.arg2, self.act2, self.dz2, f.gradient("conv2/biases"), batch=B, lrn=s.lrn); n += 1
+            native.unpool2(self.dp2, self.arg2, self.act2, self.dz2, self._g("conv2/biases"), batch=B, lrn=s.lrn); n += 1
         self._mark("unpool2")
         # dgrad first: it and wgrad both need > 113 KB of shared memory and cannot share an SM, so launching them together
         # only serialises them.  conv1_wgrad (26 KB, CUDA cores) does co-reside with the tensor-core wgrad.
@@ -348,8 +371,8 @@ class NativeEngine:
         self._mark("conv2_dgrad")
         fused_wgrad = self._fused_wgrad and x.dtype == torch.uint8 and self._on("conv2_wgrad") and self._on("conv1_wgrad")
         if fused_wgrad:
-            native.conv_wgrad_fused(self.p1, self.dz2, x, self.dpool1, self.arg1, f.gradient("conv2/weights"),
-                                    f.gradient("conv1/weights"), f.gradient("conv1/biases"), batch=B); n += 1
+            native.conv_wgrad_fused(self.p1, self.dz2, x, self.dpool1, self.arg1, self._g("conv2/weights"),
+                                    self._g("conv1/weights"), self._g("conv1/biases"), batch=B); n += 1
         else:
             # conv2_wgrad is the longer of the two weight-gradient kernels: it stays on the main stream (programmatic edge
             # from dgrad, no cross-stream hand-off on the critical path); conv1_wgrad (26 KB of smem, CUDA cores) co-resides
@@ -357,11 +380,11 @@ class NativeEngine:
             self._side.wait_event(self._fork_ev[2])
             with torch.cuda.stream(self._stream(self._side)):
                 if self._on("conv1_wgrad"):
-                    native.conv1_wgrad(x, self.dpool1, self.arg1, f.gradient("conv1/weights"), f.gradient("conv1/biases"),
+                    native.conv1_wgrad(x, self.dpool1, self.arg1, self._g("conv1/weights"), self._g("conv1/biases"),
                                        channels=s.channels); n += 1
                 self._fork_ev[3].record(self._side)
             if self._on("conv2_wgrad"):
-                native.conv2_wgrad(self.p1, self.dz2, f.gradient("conv2/weights"), batch=B); n += 1
+                native.conv2_wgrad(self.p1, self.dz2, self._g("conv2/weights"), batch=B); n += 1
         self._mark("conv1_wgrad")
         main.wait_event(self._fork_ev[1])
         if not fused_wgrad:
@@ -383,7 +406,10 @@ class NativeEngine:
         lo, hi = self.buckets[1] if getattr(self, "_early_update_done", False) else (0, f.total)
         if not self._on("update1"):
             return
-        if self.sharded:
+        if self.sharded and self._replicated_conv and getattr(self, "_early_update_done", False):
+            now, prev = (self._grad_alt_buf, f.grad) if self._parity else (self.comm.grad_buf, self.grad_alt)
+            self.comm.replicated_update(self.cfg, self.state, f, lo, hi, now, prev, finish=True)
+        elif self.sharded:
             self.comm.fused_allreduce_update(self.cfg, self.state, f, lo, hi, finish=True)
         else:
             native.fused_update_range(self.cfg, self.state, f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, lo, hi, finish=True)
@@ -413,10 +439,13 @@ class NativeEngine:
     def train_step(self, slot: int = 0) -> None:
         """Run one optimisation step on the batch staged in ``slot`` (asynchronous; no host sync)."""
         self._last_slot = slot
+        key = (slot, self._parity)
         if not self.use_graph:
             self.launches_per_step = self._step_body(slot)
+            if self._replicated_conv:
+                self._parity ^= 1
             return
-        g = self._graphs.get(slot)
+        g = self._graphs.get(key)
         if g is None:
             # warm-up outside capture (sets kernel attributes), then undo its effect on the state by re-capturing
             snap = self._snapshot()
@@ -442,17 +471,19 @@ class NativeEngine:
             self._restore(snap)
             if lockstep:
                 plane.barrier()
-            self._graphs[slot] = g
+            self._graphs[key] = g
         g.replay()
+        if self._replicated_conv:
+            self._parity ^= 1
 
     def _snapshot(self):
         f = self.flat
-        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state, self.w2_fwd, self.w2_dgrad]
+        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state, self.w2_fwd, self.w2_dgrad, self.grad_alt]
         return [b.clone() if b is not None else None for b in bufs]
 
     def _restore(self, snap) -> None:
         f = self.flat
-        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state, self.w2_fwd, self.w2_dgrad]
+        bufs = [f.w, f.grad, f.slot0, f.slot1, f.ema, f.w_bf16, self.state, self.w2_fwd, self.w2_dgrad, self.grad_alt]
         for b, s in zip(bufs, snap):
             if b is not None:
                 b.copy_(s)
@@ -510,17 +541,28 @@ class NativeEngine:
         """Tensors for the chief's summaries (main.py:95-109).  Gradients are recomputed on the last batch with an extra
         forward/backward pass: the fused update kernel clears accumulated gradients as it consumes them.
 
-        Multi-GPU: only the chief calls this, while its peers have already launched their next step.  That is safe for one
-        reason only: a peer's next exchange kernel waits in its first cross-GPU barrier until the chief launches the matching
-        kernel, and no peer reads the chief's gradient buffer before that barrier - so the buffer is private to this rank for
-        the duration of this call.  The device must therefore be idle on entry (nothing of the previous step may still be
-        reducing out of ``flat.grad``): the synchronize below enforces it instead of relying on the caller."""
+        Multi-GPU: only the chief calls this, while its peers have already launched their next step - and a slower peer may
+        still be summing the chief's gradients of the step that just ended.  The extra pass therefore accumulates into a
+        private gradient buffer, never into the buffers the exchange kernels read."""
         slot = getattr(self, "_last_slot", 0)
         torch.cuda.synchronize(self.device)
-        self.flat.grad.zero_()
-        self.forward_backward(slot)
-        grads = {v.name: self.flat.gradient(v.name).clone() for v in self.spec.variables}
-        self.flat.grad.zero_()
+        if self.sharded:
+            # never the exchanged buffers: a slower peer may still be summing this rank's gradients of the last step
+            if getattr(self, "_summary_grad", None) is None:
+                self._summary_grad = torch.zeros_like(self.flat.grad)
+            self._summary_grad.zero_()
+            self._grad_base = self._summary_grad
+            try:
+                self.forward_backward(slot)
+            finally:
+                self._grad_base = None
+            base = self._summary_grad
+            grads = {v.name: base[self.flat.offsets[v.name]:self.flat.offsets[v.name] + v.size].view(v.shape).clone() for v in self.spec.variables}
+        else:
+            self.flat.grad.zero_()
+            self.forward_backward(slot)
+            grads = {v.name: self.flat.gradient(v.name).clone() for v in self.spec.variables}
+            self.flat.grad.zero_()
         # the bf16 shadow is current on every rank even where the fp32 master lives elsewhere (sharded fc matrices)
         params = {v.name: (self.flat.weight_bf16(v.name).float() if self.sharded and v.tensor_core_only else self.flat.weight(v.name))
                   for v in self.spec.variables}

@@ -281,6 +281,13 @@ int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_update_config*
  * pointers).  mode 0 one-shot -> out (local); mode 1 two-shot, in place in every rank's buffer (+ copy to out).
  * mc_buf: NVLS multicast address of the same buffer or NULL; when set, mode 0 reads every element with one in-switch
  * reduction and mode 1 reduces its shard in the switch and multicasts the sums back. */
+/* Small buckets (the conv variables): every rank sums ALL ranks' gradients of grad[lo:hi) itself (fixed rank order) and
+ * updates its own replica - one cross-GPU barrier, no all-gather, ordinary launch.  grad_now_dev: device array of the N
+ * ranks' gradient buffers of THIS step; grad_prev_local: this rank's buffer of the previous step, cleared here (gradients
+ * of the bucket are double-buffered by step parity), or NULL.  Replaces the Apply ops of mnist_input.py:262-264. */
+int dtm_replicated_allreduce_update(const dtm_peer_ctx* ctx, const dtm_update_config* cfg, dtm_train_state* state, int lo, int hi,
+                                    float* const* grad_now_dev, float* grad_prev_local, float* slot0, float* slot1, float* ema,
+                                    void* w_bf16, void* ctrl, int do_finish, void* stream);
 int dtm_allreduce_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, float* mc_buf, int off, int n, float* out, int mode,
                       void* ctrl, void* stream);
 int dtm_broadcast_f32(const dtm_peer_ctx* ctx, float* const* bufs_dev, int off, int n, int root, void* ctrl, void* stream);
