@@ -321,12 +321,13 @@ def main() -> None:
             s_grad = f.total * 4.0
             s_gather = sum((2.0 if v.tensor_core_only else 4.0) * ((v.size + 63) // 64 * 64) for v in spec.variables)
             n = world
-            if comm.nvls:   # multimem.ld_reduce pulls every rank's copy through the switch; multimem.st is replicated by it
+            nvls = comm.use_multicast
+            if nvls:   # multimem.ld_reduce pulls every rank's copy through the switch; multimem.st is replicated by it
                 own = max(s_grad + s_gather / n, s_grad / n + s_gather)
             else:
                 own = (n - 1) / n * (s_grad + s_gather)
             roof_us = own / NVLINK_BYTES_PER_SEC * 1e6
-            out["fused_exchange"] = {"us": round(us, 2), "transport": "nvls" if comm.nvls else "p2p", "gradient_bytes": int(s_grad),
+            out["fused_exchange"] = {"us": round(us, 2), "transport": "nvls" if nvls else "p2p", "gradient_bytes": int(s_grad),
                                      "own_bytes_busier_direction": int(own), "own_bytes_roofline_us": round(roof_us, 2),
                                      "fraction_of_roofline": round(roof_us / us, 3)}
         if comm is not None:

@@ -289,7 +289,7 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
           if (d0) mc_st_bf16x8(static_cast<__nv_bfloat16*>(ctx.mc_w_bf16) + i, p0.x, p0.y, p1.x, p1.y);
         }
     }
-  } else if (N == 8 || N == 4 || N == 2) {
+  } else if (!LIGHT && (N == 8 || N == 4 || N == 2)) {
     // two float4 per thread and iteration: 2(N-1) NVLink round trips overlap, and the second one hides the optimizer
     // math of the first
     for (int base = s_lo + tid * 4; base < s_hi; base += step * 2) {
@@ -598,6 +598,10 @@ extern "C" int dtm_fused_allreduce_update(const dtm_peer_ctx* ctx, const dtm_upd
   const bool light = static_cast<size_t>(hi - lo) / ctx->world <= (2u << 20);
   if (nvls && light)
     return launch_cooperative(fused_allreduce_update_kernel<true, true>, comm_grid(static_cast<size_t>(hi - lo), max_ctas, 256), 256,
+                              static_cast<cudaStream_t>(stream), true, *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
+                              static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
+  if (!nvls && light && ctx->world <= 4)      // small-footprint P2P form (co-resident with the conv backward, like NVLS light)
+    return launch_cooperative(fused_allreduce_update_kernel<false, true>, comm_grid(static_cast<size_t>(hi - lo), max_ctas, 256), 256,
                               static_cast<cudaStream_t>(stream), true, *ctx, *cfg, state, lo, hi, slot0, slot1, ema,
                               static_cast<__nv_bfloat16*>(w_bf16), static_cast<CommCtrl*>(ctrl), do_finish, comm_depth());
   if (nvls)

@@ -281,9 +281,12 @@ class PeerComm:
         # with the conv backward (2 GPUs: 222 -> 189 us per step against a 64-CTA cap); P2P kernel (512 threads, cannot
         # share an SM with conv2_dgrad): 64 CTAs.
         if overlap_ctas is None:
-            overlap_ctas = 0 if self.nvls else 64
+            overlap_ctas = 0 if (self.nvls or self.world_size <= 4) else 64
         self.overlap_ctas = int(os.environ.get("DTM_OVERLAP_CTAS", overlap_ctas))
-        self.use_multicast = self.nvls                    # the fused update takes the NVLS path (A/B switch for tools)
+        # the fused update takes the NVLS path (A/B switch for tools).  Two ranks: the in-switch reduction has nothing to save
+        # (one peer) and its latency is higher than a peer load - measured 67 vs 40 us for the 13 MB exchange - so P2P is the
+        # default there unless DTM_NVLS=1 insists
+        self.use_multicast = self.nvls and (self.world_size > 2 or os.environ.get("DTM_NVLS", "auto").lower() in ("1", "on", "true", "yes", "force"))
         self._buffers: list[SymmetricBuffer] = []
         self.flags = self._alloc(MAX_RANKS * 4 * 16)          # epochs, padded
         self.ctrl = torch.zeros(16, dtype=torch.uint8, device=self.device)
