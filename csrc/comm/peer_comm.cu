@@ -266,28 +266,20 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   };
   const int step = nthreads * 4;
   if (nvls) {
-    // a thread owns 8 consecutive elements per visit (shard and segment borders are multiples of 64): two in-switch
-    // reductions in flight per visit, U visits in flight, and ONE 16-byte multicast store of the packed bf16 weights
-    constexpr int U = LIGHT ? 1 : 2;
-    const int nvis = LIGHT ? 1 : (depth >= 2 ? 2 : 1);
-    const int step8 = nthreads * 8;
-    for (int base = s_lo + tid * 8; base < s_hi; base += step8 * nvis) {
-      float4 g[2 * U];
+    // `depth` (<= U) in-switch reductions in flight per thread before the first one is consumed.  Consecutive threads take
+    // consecutive float4: a warp's multimem.ld_reduce covers 512 contiguous bytes.  (Measured in round 2: giving each thread
+    // 8 consecutive elements - two 16-byte reductions 32 bytes apart per lane, for the sake of one 16-byte bf16 multicast
+    // store - nearly halves the switch throughput: wide exchange 207 -> 342 us at 8 GPUs.  Reverted.)
+    constexpr int U = LIGHT ? 2 : 4;
+    depth = LIGHT ? (depth > U ? U : depth) : U;
+    for (int base = s_lo + tid * 4; base < s_hi; base += step * depth) {
+      float4 g[U];
 #pragma unroll
       for (int k = 0; k < U; ++k)
-        if (k < nvis && base + k * step8 < s_hi) {
-          g[2 * k] = mc_ld_reduce_v4(ctx.mc_grad + base + k * step8);
-          g[2 * k + 1] = mc_ld_reduce_v4(ctx.mc_grad + base + k * step8 + 4);
-        }
+        if (k < depth && base + k * step < s_hi) g[k] = mc_ld_reduce_v4(ctx.mc_grad + base + k * step);
 #pragma unroll
       for (int k = 0; k < U; ++k)
-        if (k < nvis && base + k * step8 < s_hi) {
-          const int i = base + k * step8;
-          uint2 p0 = make_uint2(0, 0), p1 = make_uint2(0, 0);
-          const bool d0 = apply(i, g[2 * k], true, p0);
-          apply(i + 4, g[2 * k + 1], true, p1);
-          if (d0) mc_st_bf16x8(static_cast<__nv_bfloat16*>(ctx.mc_w_bf16) + i, p0.x, p0.y, p1.x, p1.y);
-        }
+        if (k < depth && base + k * step < s_hi) { uint2 unused; apply(base + k * step, g[k], false, unused); }
     }
   } else if (!LIGHT && (N == 8 || N == 4 || N == 2)) {
     // two float4 per thread and iteration: 2(N-1) NVLink round trips overlap, and the second one hides the optimizer
@@ -527,8 +519,8 @@ static int comm_grid(size_t elems, int max_ctas = 0, int threads = 512) {
   return static_cast<int>(want > static_cast<size_t>(cap) ? cap : want);
 }
 
-// visits (8 elements = two multimem.ld_reduce) in flight per thread in the heavy NVLS instantiation: DTM_COMM_DEPTH = 1 | 2
-// (values above 2 are clamped - the round-1 8-GPU sweep found 4 and 8 slower; the light instantiation always uses 1)
+// in-flight multimem.ld_reduce per thread in the LIGHT NVLS instantiation: DTM_COMM_DEPTH = 1 | 2 (clamped; the heavy
+// instantiation always keeps 4 in flight - round-1 8-GPU sweep: profiles/fused_exchange_8gpu_sweep_r1.json)
 static int comm_depth() {
   const char* e = getenv("DTM_COMM_DEPTH");   // read per launch (cheap) so that tools can sweep it inside one process
   const int v = e ? atoi(e) : 2;

@@ -167,59 +167,85 @@ struct Loader {
     enough.notify_all();
   }
 
-  void produce(uint64_t thread_seed) {
-    std::mt19937_64 rng(thread_seed);
-    std::vector<uint8_t> buf;
-    while (!stop.load()) {
-      std::vector<std::string> order = files;
-      if (shuffle) std::shuffle(order.begin(), order.end(), rng);
-      uint64_t n = 0;
-      for (const std::string& path : order) {
-        FILE* f = fopen(path.c_str(), "rb");
-        if (!f) { fail("Failed to find file: " + path); return; }
-        for (;;) {
-          uint8_t hdr[12];
-          const size_t got = fread(hdr, 1, 12, f);
-          if (got == 0) break;                         // clean end of file
-          if (got != 12) { fclose(f); fail("truncated TFRecord header in " + path); return; }
-          uint64_t len;
-          uint32_t len_crc;
-          memcpy(&len, hdr, 8);
-          memcpy(&len_crc, hdr + 8, 4);
-          if (masked_crc(hdr, 8) != len_crc) { fclose(f); fail("corrupt TFRecord length in " + path); return; }
-          if (len > (1ull << 30)) { fclose(f); fail("implausible TFRecord length in " + path); return; }
-          buf.resize(len + 4);
-          if (fread(buf.data(), 1, len + 4, f) != len + 4) { fclose(f); fail("truncated TFRecord in " + path); return; }
-          uint32_t data_crc;
-          memcpy(&data_crc, buf.data() + len, 4);
-          if (masked_crc(buf.data(), len) != data_crc) { fclose(f); fail("corrupt TFRecord payload in " + path); return; }
-          const uint8_t* img = nullptr;
-          size_t img_len = 0;
-          int64_t label = 0;
-          if (!parse_example(buf.data(), len, &img, &img_len, &label)) {
-            fclose(f); fail("record without image_raw/label features in " + path); return;
-          }
-          if (static_cast<int>(img_len) != image_bytes) {
-            fclose(f);
-            fail("record holds " + std::to_string(img_len) + " image bytes, expected " + std::to_string(image_bytes));
-            return;
-          }
-          ++n;
-          std::unique_lock<std::mutex> lk(mu);
-          not_full.wait(lk, [&] { return stop.load() || !free_slots.empty(); });
-          if (stop.load()) { fclose(f); return; }
-          const int slot = free_slots.back();
-          free_slots.pop_back();
-          memcpy(slab.data() + static_cast<size_t>(slot) * image_bytes, img, image_bytes);
-          labels[slot] = static_cast<int32_t>(label);
-          filled.push_back(slot);
-          ++records_read;
-          if (static_cast<int>(filled.size()) > min_after) enough.notify_one();
+  // ONE record stream for all reader threads, like the reference's single TFRecordReader behind its filename queue
+  // (mnist_input.py:57-71): a thread takes the next raw record under `read_mu` (framing + both CRCs), then parses the Example
+  // and fills the shuffle queue on its own - every record is delivered once per epoch, whichever thread asks.
+  std::mutex read_mu;
+  FILE* cur = nullptr;
+  std::string cur_path;
+  std::vector<std::string> order;
+  size_t next_file = 0;
+  uint64_t epoch_records = 0;
+  bool first_epoch = true;
+  std::mt19937_64 file_rng;
+
+  // false: stop requested or error recorded
+  bool next_record(std::vector<uint8_t>& buf, uint64_t* len_out) {
+    std::lock_guard<std::mutex> rl(read_mu);
+    for (;;) {
+      if (stop.load()) return false;
+      if (!cur) {
+        if (next_file == order.size()) {          // epoch boundary
+          if (!first_epoch && epoch_records == 0) { fail("input files contain no records"); return false; }
+          first_epoch = false;
+          order = files;
+          if (shuffle) std::shuffle(order.begin(), order.end(), file_rng);
+          next_file = 0;
+          epoch_records = 0;
         }
-        fclose(f);
+        cur_path = order[next_file++];
+        cur = fopen(cur_path.c_str(), "rb");
+        if (!cur) { fail("Failed to find file: " + cur_path); return false; }
       }
-      if (n == 0) { fail("input files contain no records"); return; }
+      uint8_t hdr[12];
+      const size_t got = fread(hdr, 1, 12, cur);
+      if (got == 0) { fclose(cur); cur = nullptr; continue; }     // clean end of file
+      auto bad = [&](const std::string& what) { fclose(cur); cur = nullptr; fail(what + cur_path); return false; };
+      if (got != 12) return bad("truncated TFRecord header in ");
+      uint64_t len;
+      uint32_t len_crc;
+      memcpy(&len, hdr, 8);
+      memcpy(&len_crc, hdr + 8, 4);
+      if (masked_crc(hdr, 8) != len_crc) return bad("corrupt TFRecord length in ");
+      if (len > (1ull << 30)) return bad("implausible TFRecord length in ");
+      buf.resize(len + 4);
+      if (fread(buf.data(), 1, len + 4, cur) != len + 4) return bad("truncated TFRecord in ");
+      uint32_t data_crc;
+      memcpy(&data_crc, buf.data() + len, 4);
+      if (masked_crc(buf.data(), len) != data_crc) return bad("corrupt TFRecord payload in ");
+      ++epoch_records;
+      *len_out = len;
+      return true;
     }
+  }
+
+  void produce() {
+    std::vector<uint8_t> buf;
+    uint64_t len = 0;
+    while (next_record(buf, &len)) {
+      const uint8_t* img = nullptr;
+      size_t img_len = 0;
+      int64_t label = 0;
+      if (!parse_example(buf.data(), len, &img, &img_len, &label)) { fail("record without image_raw/label features in " + cur_path); return; }
+      if (static_cast<int>(img_len) != image_bytes) {
+        fail("record holds " + std::to_string(img_len) + " image bytes, expected " + std::to_string(image_bytes));
+        return;
+      }
+      std::unique_lock<std::mutex> lk(mu);
+      not_full.wait(lk, [&] { return stop.load() || !free_slots.empty(); });
+      if (stop.load()) return;
+      const int slot = free_slots.back();
+      free_slots.pop_back();
+      memcpy(slab.data() + static_cast<size_t>(slot) * image_bytes, img, image_bytes);
+      labels[slot] = static_cast<int32_t>(label);
+      filled.push_back(slot);
+      ++records_read;
+      if (static_cast<int>(filled.size()) > min_after) enough.notify_one();
+    }
+  }
+
+  ~Loader() {
+    if (cur) fclose(cur);
   }
 };
 
@@ -254,7 +280,8 @@ extern "C" void* dtm_loader_create(const char* const* files, int n_files, int ba
   L->consumer_rng.seed(seed);
   // without shuffling the order must be the file order: one reader
   const int nthreads = L->shuffle ? (num_threads < 1 ? 1 : num_threads) : 1;
-  for (int t = 0; t < nthreads; ++t) L->threads.emplace_back([L, t, seed] { L->produce(seed + 1 + t); });
+  L->file_rng.seed(seed + 1);
+  for (int t = 0; t < nthreads; ++t) L->threads.emplace_back([L] { L->produce(); });
   return L;
 }
 

@@ -12,7 +12,7 @@ namespace dtm {
 
 // Grid-stride form (every CTA owns a fixed 1/grid share).  Default: measured faster than the chunk dispenser below both
 // stand-alone (18.7 vs 20.8 us uncapped, 26.9 vs 29.8 us at one CTA per SM) and inside the step.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(512)
 fused_update_stride_kernel(const dtm_update_config cfg, dtm_train_state* __restrict__ st, float* __restrict__ w,
                     float* __restrict__ grad, float* __restrict__ slot0, float* __restrict__ slot1,
                     float* __restrict__ ema, __nv_bfloat16* __restrict__ w_bf16, float grad_scale, int lo, int hi,
@@ -168,9 +168,17 @@ extern "C" int dtm_fused_update_range(const dtm_update_config* cfg, dtm_train_st
   if (grid < 1) grid = 1;
   if (cfg->pack_seg >= cfg->n_segments || (cfg->pack_seg >= 0 && (!cfg->pack_fwd || !cfg->pack_dgrad)))
     return dtm_fail("fused_update: pack_seg set without both pack buffers");
+  // threads per CTA of the capped (max_ctas) grid-stride form: more warps = more loads in flight next to the conv backward
+  // kernels; 384 x 40 registers still fits beside a 384 x 128-register conv2_dgrad CTA (DTM_UPDATE_THREADS=256|384|512)
+  int threads = 256;
+  if (!dynamic && max_ctas > 0) {
+    const char* te = getenv("DTM_UPDATE_THREADS");
+    const int tv = te ? atoi(te) : 256;
+    threads = (tv == 384 || tv == 512) ? tv : 256;
+  }
   cudaLaunchConfig_t lc = {};
   lc.gridDim = dim3(grid);
-  lc.blockDim = dim3(256);
+  lc.blockDim = dim3(threads);
   lc.stream = s;
   cudaLaunchAttribute attr[1];
   if (const L2Window* win = update_l2_window()) {   // optimizer state stays in the persisting L2 between steps

@@ -142,33 +142,42 @@ class TFRecordBatches:
         self._stop = threading.Event()
         self._err: list[BaseException] = []
         if not shuffle:
-            num_threads = 1          # several readers would interleave (and repeat) the file order
+            num_threads = 1          # several parsers would interleave the file order
+        self._file_seed = seed + 1
+        self._read_lock = threading.Lock()
+        self._stream = self._raw_records()
         self._threads = [threading.Thread(target=self._produce, args=(seed + 1 + i,), daemon=True) for i in range(num_threads)]
         for t in self._threads:
             t.start()
 
+    def _raw_records(self):
+        """ONE record stream for all producer threads, like the reference's single TFRecordReader behind its filename queue
+        (mnist_input.py:57-71): every record is delivered once per epoch, whichever thread asks."""
+        rng = random.Random(self._file_seed)
+        while True:
+            files = list(self.filenames)
+            if self.shuffle:
+                rng.shuffle(files)
+            n = 0
+            for f in files:
+                for rec in read_records(f):
+                    n += 1
+                    yield rec
+            if n == 0:
+                raise ValueError("input files contain no records")
+
     def _produce(self, seed: int) -> None:
-        rng = random.Random(seed)
         try:
             while not self._stop.is_set():
-                files = list(self.filenames)
-                if self.shuffle:
-                    rng.shuffle(files)
-                n = 0
-                for f in files:
-                    for rec in read_records(f):
-                        item = parse_record(rec, self.image_bytes)
-                        n += 1
-                        while not self._stop.is_set():
-                            try:
-                                self._q.put(item, timeout=0.1)
-                                break
-                            except queue.Full:
-                                continue
-                        if self._stop.is_set():
-                            return
-                if n == 0:
-                    raise ValueError("input files contain no records")
+                with self._read_lock:
+                    rec = next(self._stream)
+                item = parse_record(rec, self.image_bytes)
+                while not self._stop.is_set():
+                    try:
+                        self._q.put(item, timeout=0.1)
+                        break
+                    except queue.Full:
+                        continue
         except BaseException as e:  # surfaced to the consumer
             self._err.append(e)
 

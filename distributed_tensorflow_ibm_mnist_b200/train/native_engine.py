@@ -106,10 +106,17 @@ class NativeEngine:
         # us).  No cap for wide (the update is the long pole) nor for the LRN preset (measured slower: 406 -> 429 us).
         sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self._early_update_ctas = int(env.get("DTM_EARLY_UPDATE_CTAS", str(sm_count if (small and not spec.lrn) else 0)))
-        if comm is not None and not small and "DTM_OVERLAP_CTAS" not in env:
-            # wide: the fc bucket's exchange runs ~200 us and is bound by the NVSwitch, not by the CTA count (8-GPU sweep:
-            # 32 CTAs reach the time of 148) - leave most SMs entirely to the conv backward
-            comm.overlap_ctas = 64
+        if comm is not None and "DTM_OVERLAP_CTAS" not in env:
+            if not small:
+                # wide: the fc bucket's exchange runs ~200 us and is bound by the NVSwitch, not by the CTA count (8-GPU
+                # sweep: 32 CTAs reach the time of 148) - leave most SMs entirely to the conv backward
+                comm.overlap_ctas = 64
+            else:
+                # the overlapped exchange shares its SMs with the conv backward: give it only as many CTAs as the rank's
+                # shard needs (about six 256-thread visits per CTA).  8 GPUs, same box: 148 CTAs 167.7 us per step,
+                # 64 CTAs 153.4, 32 CTAs 163.0; two ranks (four times the shard) want every SM
+                shard4 = (self.flat.total - self.flat.offsets["local3/weights"]) // self.world // 4
+                comm.overlap_ctas = max(32, min(sm_count, -(-shard4 // (256 * 6))))
         # one tcgen05 kernel for both convolution weight gradients (conv1's operands are built by the warps that idle in
         # conv2_wgrad): single-channel uint8 input only; DTM_WGRAD_FUSED=0 restores the two separate kernels.  Pays off
         # together with the persisting-L2 optimizer state (profiles/ab_wgrad_update_r2.md): 152.6 vs 157.6 us per step
@@ -177,6 +184,12 @@ class NativeEngine:
         native.conv2_pack_weights(self.flat.weight_bf16("conv2/weights"), self.w2_fwd, self.w2_dgrad)
         if int(self.read_state().global_step) == 0 and self.flat.ema is not None:
             self.flat.ema.copy_(self.flat.w)     # TF initialises the shadows to the (now common) initial values
+        elif self.flat.ema is not None:
+            # a restored run: optimizer slots and EMA shadows must be the root's as well - only the root may have seen the
+            # checkpoint (train_dir on a local disk), and a rank with fresh slots would silently corrupt its shard
+            for buf in (self.flat.slot0, self.flat.slot1, self.flat.ema):
+                if buf is not None:
+                    self.comm.plane.broadcast_tensor(buf, root)
         torch.cuda.synchronize(self.device)
 
     @property
