@@ -173,7 +173,7 @@ extern "C" int dtm_fused_update_range(const dtm_update_config* cfg, dtm_train_st
   int threads = 256;
   if (!dynamic && max_ctas > 0) {
     const char* te = getenv("DTM_UPDATE_THREADS");
-    const int tv = te ? atoi(te) : 256;
+    const int tv = te ? atoi(te) : 384;   // same box: 256 -> 153.0, 384 -> 147.8, 512 -> 147.9 us per step
     threads = (tv == 384 || tv == 512) ? tv : 256;
   }
   cudaLaunchConfig_t lc = {};
