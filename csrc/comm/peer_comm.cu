@@ -113,7 +113,8 @@ DTM_DEVICE void barrier_ready(const dtm_peer_ctx& ctx, unsigned int k) {
   barrier_ready_publish(ctx, k);
   barrier_ready_wait(ctx, k);
 }
-DTM_DEVICE void barrier_done(const dtm_peer_ctx& ctx, CommCtrl* ctrl, unsigned int k) {
+// The last CTA of the grid to get here publishes epoch `k` to every peer (all CTAs call it; no waiting).
+DTM_DEVICE void publish_when_grid_arrived(const dtm_peer_ctx& ctx, CommCtrl* ctrl, unsigned int k) {
   __shared__ unsigned int s_publish;
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -121,10 +122,13 @@ DTM_DEVICE void barrier_done(const dtm_peer_ctx& ctx, CommCtrl* ctrl, unsigned i
     unsigned int prev;
     asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(&ctrl->arrive) : "memory");
     s_publish = prev == gridDim.x - 1 ? 1u : 0u;
-    if (s_publish) ctrl->arrive = 0;   // nobody counts in again before this barrier has released them
+    if (s_publish) ctrl->arrive = 0;   // nobody counts in again before the peers have answered this epoch
   }
   __syncthreads();
   if (s_publish && threadIdx.x < ctx.world) st_release_sys(ctx.flags[threadIdx.x] + ctx.rank, k);
+}
+DTM_DEVICE void barrier_done(const dtm_peer_ctx& ctx, CommCtrl* ctrl, unsigned int k) {
+  publish_when_grid_arrived(ctx, ctrl, k);
   if (threadIdx.x < ctx.world) spin_until_ge_sys(ctx.flags[ctx.rank] + threadIdx.x, k, threadIdx.x);
   __syncthreads();
 }
@@ -182,7 +186,13 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   pdl_wait();                 // launched with a programmatic edge: the launch latency hides under the preceding kernel's tail
   pdl_launch_dependents();
   const unsigned int e0 = ld_acquire_gpu(&ctrl->epoch);
-  barrier_ready_publish(ctx, e0 + 1);      // my gradients are complete: tell the peers before anything else
+  // "My gradients are complete" may be told to the peers at once - unless this launch first sums squares of weights
+  // (weight-decay loss terms): a peer that has seen the flag may already multicast NEW weights into the very copies that
+  // sum is reading, so then the flag goes out only after every CTA has finished the sum.
+  bool prepass = false;
+  for (int s = 0; s < cfg.n_segments; ++s)
+    prepass = prepass || (cfg.seg_wd[s] != 0.0f && max(lo, cfg.seg_offset[s]) < min(hi, cfg.seg_offset[s + 1]));
+  if (!prepass) barrier_ready_publish(ctx, e0 + 1);
   const UpdateScalars u = make_update_scalars(cfg, st, 1.0f / static_cast<float>(N));
   float* w_local = ctx.w[r];
   float* g_local = ctx.grad[r];
@@ -224,6 +234,7 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
   }
 
   // ---- barrier A: every rank's gradients are complete
+  if (prepass) publish_when_grid_arrived(ctx, ctrl, e0 + 1);
   barrier_ready_wait(ctx, e0 + 1);
 
   // ---- reduce-scatter + optimizer on my shard + all-gather of the new weights

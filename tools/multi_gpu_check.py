@@ -71,6 +71,10 @@ def main() -> int:
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         good = bool(flag.item())
         ok = ok and good
+        if not good:       # which rank, and what it saw
+            every = [None] * world
+            dist.all_gather_object(every, (bool(cond), repr(info)))
+            info = {"per_rank": every}
         report["checks"][name] = {"pass": good, "info": info}
         if rank == 0:
             print(f"[check] {name}: {'PASS' if good else 'FAIL'} {info if info is not None else ''}", flush=True)
@@ -141,7 +145,8 @@ def main() -> int:
         check(f"fused_update_{kind}_ema_shard", e_err < tol, e_err)
         sa, sb = native.read_state(st_a), native.read_state(st_b)
         check(f"fused_update_{kind}_state", sa.global_step == sb.global_step == 3 and abs(sa.last_lr - sb.last_lr) < 1e-9 and
-              abs(sa.last_wl[4] - sb.last_wl[4]) <= 2e-3 * abs(sb.last_wl[4]) + 1e-9, (sa.global_step, sa.last_wl[4], sb.last_wl[4]))
+              abs(sa.last_wl[4] - sb.last_wl[4]) <= 2e-3 * abs(sb.last_wl[4]) + 1e-9,
+              (sa.global_step, sb.global_step, sa.last_wl[4], sb.last_wl[4], sa.last_lr, sb.last_lr))
         zero_ok = float(flat_a.gradient("conv2/weights").abs().sum()) == 0.0 and float(flat_a.gradient("local3/weights").abs().sum()) > 0
         check(f"fused_update_{kind}_grad_clearing", zero_ok)
         w0 = flat_a.w_bf16.clone()
