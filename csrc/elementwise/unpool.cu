@@ -60,8 +60,10 @@ unpool2_kernel(const __nv_bfloat16* __restrict__ dp2, const uint8_t* __restrict_
   }
 }
 
-// reference preset: one thread per pixel, all 64 channels in registers.
-__global__ void __launch_bounds__(128)
+// reference preset.  Eight lanes per pixel, eight channels per lane: the +-4-channel LRN windows reach into the two
+// neighbouring lanes only, so the window sums need eight shuffles instead of 64 channels in one thread's registers (round 1:
+// one thread per pixel, 255 registers with spills, 88 us for 100 K pixels).
+__global__ void __launch_bounds__(256)
 unpool2_lrn_kernel(const __nv_bfloat16* __restrict__ dp2, const uint8_t* __restrict__ argmax,
                    const __nv_bfloat16* __restrict__ act2, int batch, uint8_t* __restrict__ dz2_planes,
                    float* __restrict__ db2) {
@@ -70,19 +72,27 @@ unpool2_lrn_kernel(const __nv_bfloat16* __restrict__ dp2, const uint8_t* __restr
   __syncthreads();
   pdl_wait();
   pdl_launch_dependents();
-  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool active = pix < batch * IMG * IMG;
-  float g[UP_C];
-  if (active) {
-    const int img = pix / (IMG * IMG), p = pix % (IMG * IMG);
-    const int h = p / IMG, w = p % IMG;
-    const uint32_t mypos = (h & 1) * 2 + (w & 1);
-    const size_t prow = (static_cast<size_t>(img) * 49 + (h >> 1) * 7 + (w >> 1)) * UP_C;
-    float a[UP_C];
+  const int c8 = threadIdx.x & 7;
+  const int total = batch * IMG * IMG;
+  const float alpha = 0.001f / 9.0f, beta = 0.75f;
+  float dbp[8];
 #pragma unroll
-    for (int c8 = 0; c8 < 8; ++c8) {
-      const uint4 gv = *reinterpret_cast<const uint4*>(dp2 + prow + c8 * 8);
-      const uint2 av = *reinterpret_cast<const uint2*>(argmax + prow + c8 * 8);
+  for (int i = 0; i < 8; ++i) dbp[i] = 0.0f;
+  // every lane of a warp runs the same number of rounds (the shuffles need all 32 lanes)
+  for (int base = blockIdx.x * 32; base < total; base += gridDim.x * 32) {
+    const int pix = base + (threadIdx.x >> 3);
+    const bool active = pix < total;
+    float g[8], a[8];
+    int img = 0, h = 0, w = 0;
+    if (active) {
+      img = pix / (IMG * IMG);
+      const int p = pix - img * (IMG * IMG);
+      h = p / IMG;
+      w = p - h * IMG;
+      const uint32_t mypos = (h & 1) * 2 + (w & 1);
+      const size_t prow = (static_cast<size_t>(img) * 49 + (h >> 1) * 7 + (w >> 1)) * UP_C + c8 * 8;
+      const uint4 gv = *reinterpret_cast<const uint4*>(dp2 + prow);
+      const uint2 av = *reinterpret_cast<const uint2*>(argmax + prow);
       const uint4 xv = *reinterpret_cast<const uint4*>(act2 + static_cast<size_t>(pix) * UP_C + c8 * 8);
       const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w};
       const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
@@ -90,49 +100,67 @@ unpool2_lrn_kernel(const __nv_bfloat16* __restrict__ dp2, const uint8_t* __restr
       for (int i = 0; i < 4; ++i) {
         const uint32_t a0 = ((i < 2 ? av.x : av.y) >> (16 * (i & 1))) & 0xFF;
         const uint32_t a1 = ((i < 2 ? av.x : av.y) >> (16 * (i & 1) + 8)) & 0xFF;
-        g[c8 * 8 + 2 * i] = a0 == mypos ? bf16_lo(gw[i]) : 0.0f;
-        g[c8 * 8 + 2 * i + 1] = a1 == mypos ? bf16_hi(gw[i]) : 0.0f;
-        a[c8 * 8 + 2 * i] = bf16_lo(xw[i]);
-        a[c8 * 8 + 2 * i + 1] = bf16_hi(xw[i]);
+        g[2 * i] = a0 == mypos ? bf16_lo(gw[i]) : 0.0f;
+        g[2 * i + 1] = a1 == mypos ? bf16_hi(gw[i]) : 0.0f;
+        a[2 * i] = bf16_lo(xw[i]);
+        a[2 * i + 1] = bf16_hi(xw[i]);
       }
-    }
-    const float alpha = 0.001f / 9.0f, beta = 0.75f;
-    float t1[UP_C], sp[UP_C];
+    } else {
 #pragma unroll
-    for (int c = 0; c < UP_C; ++c) {
+      for (int i = 0; i < 8; ++i) { g[i] = 0.0f; a[i] = 0.0f; }
+    }
+    // ext[0..3] = left neighbour's channels 4..7, ext[4..11] = own, ext[12..15] = right neighbour's channels 0..3
+    auto widen = [&](const float (&v)[8], float (&ext)[16]) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float l = __shfl_up_sync(0xffffffffu, v[4 + i], 1);
+        const float r = __shfl_down_sync(0xffffffffu, v[i], 1);
+        ext[i] = c8 > 0 ? l : 0.0f;
+        ext[12 + i] = c8 < 7 ? r : 0.0f;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ext[4 + i] = v[i];
+    };
+    float sq[8], ext[16], t1[8], sp[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sq[i] = a[i] * a[i];
+    widen(sq, ext);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
       float s = 0.0f;
 #pragma unroll
-      for (int d = -4; d <= 4; ++d)
-        if (c + d >= 0 && c + d < UP_C) s += a[c + d] * a[c + d];
+      for (int d = 0; d < 9; ++d) s += ext[i + d];
       s = 1.0f + alpha * s;
-      const float p = __powf(s, -beta);
-      sp[c] = p;
-      t1[c] = g[c] * a[c] * p / s;
+      const float pw = __powf(s, -beta);
+      sp[i] = pw;
+      t1[i] = g[i] * a[i] * pw / s;
     }
+    widen(t1, ext);
+    float o[8];
 #pragma unroll
-    for (int j = 0; j < UP_C; ++j) {
+    for (int i = 0; i < 8; ++i) {
       float acc = 0.0f;
 #pragma unroll
-      for (int d = -4; d <= 4; ++d)
-        if (j + d >= 0 && j + d < UP_C) acc += t1[j + d];
-      const float da = g[j] * sp[j] - 2.0f * alpha * beta * a[j] * acc;
-      g[j] = a[j] > 0.0f ? da : 0.0f;
+      for (int d = 0; d < 9; ++d) acc += ext[i + d];
+      const float da = g[i] * sp[i] - 2.0f * alpha * beta * a[i] * acc;
+      o[i] = a[i] > 0.0f ? da : 0.0f;
     }
-    uint8_t* base = dz2_planes + static_cast<size_t>(img) * plane_image_bytes(UP_C);
+    if (active) {
+      uint8_t* dst = dz2_planes + static_cast<size_t>(img) * plane_image_bytes(UP_C) + plane_offset(h, w, c8 * 8);
+      const uint4 pk = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+      *reinterpret_cast<uint4*>(dst) = pk;
+      // bias gradient: the bf16-rounded values the wgrad kernel will see
+      const uint32_t pw4[4] = {pk.x, pk.y, pk.z, pk.w};
 #pragma unroll
-    for (int c8 = 0; c8 < 8; ++c8)
-      *reinterpret_cast<uint4*>(base + plane_offset(h, w, c8 * 8)) =
-          make_uint4(pack_bf16x2(g[c8 * 8], g[c8 * 8 + 1]), pack_bf16x2(g[c8 * 8 + 2], g[c8 * 8 + 3]),
-                     pack_bf16x2(g[c8 * 8 + 4], g[c8 * 8 + 5]), pack_bf16x2(g[c8 * 8 + 6], g[c8 * 8 + 7]));
-  } else {
-#pragma unroll
-    for (int j = 0; j < UP_C; ++j) g[j] = 0.0f;
+      for (int i = 0; i < 4; ++i) { dbp[2 * i] += bf16_lo(pw4[i]); dbp[2 * i + 1] += bf16_hi(pw4[i]); }
+    }
   }
-  // bias gradient: reduce the bf16-rounded values the wgrad kernel will see
 #pragma unroll
-  for (int j = 0; j < UP_C; ++j) {
-    const float s = warp_sum(__bfloat162float(__float2bfloat16(g[j])));
-    if (lane_id() == 0) atomicAdd(&s_db[j], s);
+  for (int i = 0; i < 8; ++i) {
+    float v = dbp[i];
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    if (lane_id() < 8) atomicAdd(&s_db[c8 * 8 + i], v);
   }
   __syncthreads();
   if (threadIdx.x < UP_C) red_add_f32(db2 + threadIdx.x, s_db[threadIdx.x]);
@@ -181,7 +209,8 @@ extern "C" int dtm_unpool2(const void* dp2, const void* argmax, const void* act2
   if (lrn) {
     if (!act2) return dtm_fail("unpool2: LRN backward needs act2");
     const int pixels = batch * IMG * IMG;
-    DTM_CUDA_OK(launch_pdl(unpool2_lrn_kernel, dim3((pixels + 127) / 128), dim3(128), 0, s, static_cast<const __nv_bfloat16*>(dp2),
+    const int grid = min((pixels + 31) / 32, 8 * device_sm_count());
+    DTM_CUDA_OK(launch_pdl(unpool2_lrn_kernel, dim3(grid), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(dp2),
                            static_cast<const uint8_t*>(argmax), static_cast<const __nv_bfloat16*>(act2), batch,
                            static_cast<uint8_t*>(dz2_planes), db2));
   } else {

@@ -208,6 +208,34 @@ def test_unpool2_and_conv2_backward(B):
     assert _rel_err(dw2.cpu(), want_dw) < 1e-3
 
 
+@pytest.mark.parametrize("B", [9, 130])
+def test_unpool2_lrn_backward(B):
+    """Pooling + LRN backward of the reference preset (mnist_input.py:163-172): dZ2 = relu'(a) * lrn_bwd(route(dP2)) against
+    autograd through the oracle's tf_lrn; 9 images = a partly filled last warp, 130 = several rounds per CTA."""
+    native, layouts = _native()
+    from distributed_tensorflow_ibm_mnist_b200.models.oracle import tf_lrn
+
+    g = torch.Generator().manual_seed(41 + B)
+    act = _bf(torch.relu(torch.randn(B, 14, 14, 64, generator=g)) * 3.0)
+    dp2 = _bf(torch.randn(B, 49, 64, generator=g))
+    arg = torch.randint(0, 4, (B, 49, 64), dtype=torch.uint8, generator=g)
+    dy = torch.zeros(B, 7, 2, 7, 2, 64)
+    a4 = arg.view(B, 7, 7, 64).long()
+    for d in range(4):
+        dy[:, :, d >> 1, :, d & 1, :] = torch.where(a4 == d, dp2.view(B, 7, 7, 64), torch.zeros(()))
+    dy = dy.view(B, 14, 14, 64)
+    av = act.permute(0, 3, 1, 2).clone().requires_grad_(True)
+    tf_lrn(av).backward(dy.permute(0, 3, 1, 2))
+    want = (av.grad * (av.detach() > 0)).permute(0, 2, 3, 1)
+    planes = layouts.alloc_planes(B, 64, DEV)
+    db2 = torch.zeros(64, device=DEV)
+    native.unpool2(dp2.to(torch.bfloat16).to(DEV), arg.to(DEV), act.to(torch.bfloat16).to(DEV).view(B, 196, 64), planes, db2, batch=B, lrn=True)
+    got = layouts.planes_to_nhwc(planes, 64).float().cpu()
+    assert _rel_err(got, want) < 1e-2
+    assert layouts.planes_border_is_zero(planes, 64)
+    assert _rel_err(db2.cpu(), got.sum(dim=(0, 1, 2))) < 1e-4
+
+
 def test_gemm_mask_unpool_matches_gemm_plus_unpool():
     """The fused dP2 GEMM epilogue writes the same dP2 and the same un-pooled planes as GEMM + unpool2 kernel."""
     native, layouts = _native()
