@@ -62,6 +62,11 @@ class NativeEngine:
         if self.flat.blob is not None and os.environ.get("DTM_L2_PERSIST", "1") != "0":
             try:
                 self.l2_window = native.set_update_l2_window(self.flat.blob)
+                if self.l2_window["carveout_bytes"] < self.l2_window["bytes"]:
+                    # the state does not fit the persisting carve-out (wide preset: 568 MB): a partial window only makes
+                    # the update kernels thrash the lines they pinned (measured: 497 -> 715 us per step) - switch it off
+                    native.set_update_l2_window(None)
+                    self.l2_window = None
             except _lib.NativeError:
                 self.l2_window = None
         self._graphs: dict[tuple, torch.cuda.CUDAGraph] = {}
