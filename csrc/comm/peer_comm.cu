@@ -305,7 +305,17 @@ fused_allreduce_update_kernel(const dtm_peer_ctx ctx, const dtm_update_config cf
       if (two) apply(base + step, g1, false, unused);
     }
   } else {
-    for (int i = s_lo + tid * 4; i < s_hi; i += step) { uint2 unused; apply(i, reduce_peers(ctx.grad, N, i), false, unused); }
+    // software-pipelined: the peer loads of the next visit are in flight while this one is updated (a visit is one NVLink
+    // round trip + the optimizer's local loads; with few visits per thread - 5 at two ranks - neither hides the other)
+    int i = s_lo + tid * 4;
+    float4 g_next = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < s_hi) g_next = reduce_peers(ctx.grad, N, i);
+    for (; i < s_hi; i += step) {
+      const float4 g = g_next;
+      if (i + step < s_hi) g_next = reduce_peers(ctx.grad, N, i + step);
+      uint2 unused;
+      apply(i, g, false, unused);
+    }
   }
 
   // ---- barrier B: all shards of the new weights have landed everywhere, nobody reads my gradients any more
