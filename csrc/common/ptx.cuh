@@ -308,6 +308,11 @@ DTM_DEVICE uint32_t pack_bf16x2(float lo, float hi) {
 DTM_DEVICE float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 DTM_DEVICE float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
 
+// Cache hint without a destination register: an epilogue issues it for the operands it will need BEFORE it waits for the
+// accumulator, so that the later loads hit L1/L2 instead of starting their DRAM/L2 round trip after the wait
+// (profiles/stall_report_r1.md: 10-22 % of the GEMM / dgrad stall samples sat on exactly those loads).
+DTM_DEVICE void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 DTM_DEVICE float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -7,6 +7,7 @@
 // K-chunks = 200 tcgen05.mma of shape 128 x 32 x 16.  The B operand is W2 with both spatial axes flipped and
 // (ci, co) swapped: B[k = tap'*64 + co][n = ci] = W2[24 - tap'][ci][co]; eight consecutive co are contiguous in
 // the TensorFlow layout, so the re-pack into [k/8][n][8] is one 16-byte load per chunk.
+#include <stdlib.h>
 #include "../common/ptx.cuh"
 #include "../common/host_util.h"
 #include "../../include/dtm_b200.h"
@@ -47,7 +48,7 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
 
-  if (!early_weights) pdl_wait();   // strict mode: nothing is read from global memory before the dependency wait
+  if (!(early_weights & 1)) pdl_wait();   // strict mode: nothing is read from global memory before the dependency wait
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < DG_BUFS; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
     for (int i = 0; i < DG_ACC; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 32 * DgEpi<LRN>::WARPS); }
@@ -133,6 +134,13 @@ conv2_dgrad_kernel(const uint8_t* __restrict__ dz2_planes, const __nv_bfloat16* 
     for (int u = first; u < units; u += stride, ++it) {
       const int a = it % DG_ACC;
       const int img = u >> 1;
+      {  // the activation that gates this pixel's gradient: start fetching it before the accumulator wait
+        const int hp = (u & 1) * 8 + q * 2 + h_sub;
+        if (!(early_weights & 2) && hp < IMG && w_px < IMG) {
+          if (LRN) prefetch_l1(pool_raw + (static_cast<size_t>(img) * (IMG * IMG) + hp * IMG + w_px) * DG_CI);
+          else     prefetch_l1(p1_planes + static_cast<size_t>(img) * plane_image_bytes(DG_CI) + plane_offset(hp, w_px, c0));
+        }
+      }
       mbar_wait(&acc_full[a], (it / DG_ACC) & 1, 23);
       tc_fence_after();
       do {   // single pass; `continue` below leaves it for threads whose grid pixel is padding
@@ -233,11 +241,13 @@ extern "C" int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, cons
     configured[dev_slot] = true;
   }
   const int grid = min(2 * batch, device_sm_count());
+  const char* pe = getenv("DTM_EPI_PREFETCH");          // bit 1 of the mode word: epilogue prefetch off (A/B switch)
+  const int no_prefetch = (pe && pe[0] == '0') ? 2 : 0;
   auto launch = [&](auto kern) -> int {
     DTM_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(lrn ? 256 : 384), DG_SMEM, s, static_cast<const uint8_t*>(dz2_planes),
                            static_cast<const __nv_bfloat16*>(w2_bf16), static_cast<const uint8_t*>(packed),
                            static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(pool_raw), batch,
-                           static_cast<__nv_bfloat16*>(dpool1), pdl_mode() == 2 ? 1 : 0));
+                           static_cast<__nv_bfloat16*>(dpool1), (pdl_mode() == 2 ? 1 : 0) | no_prefetch));
     return 0;
   };
   if (int rc = lrn ? launch(conv2_dgrad_kernel<true>) : launch(conv2_dgrad_kernel<false>)) return rc;

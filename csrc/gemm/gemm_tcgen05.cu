@@ -10,6 +10,7 @@
 // Either operand may be K-major (K contiguous in global memory) or MN-major (M/N contiguous); the
 // TensorFlow [in, out] weight layout therefore serves forward (B is MN-major), dX (B is K-major) and
 // dW (both MN-major) without a transposed copy.
+#include <stdlib.h>
 #include "../common/ptx.cuh"
 #include "../common/philox.cuh"
 #include "../common/host_util.h"
@@ -47,6 +48,7 @@ struct GemmArgs {
   // fp32 partial tile into CTA 0's shared memory (DSMEM), CTA 0 adds it and runs the fused epilogue.  Doubles the number
   // of SMs streaming operands when the tile count is below half the machine (the fc forward: 64 tiles, K = 3136).
   int cluster_reduce;
+  int prefetch;                 // epilogue operand prefetch before the accumulator wait (DTM_EPI_PREFETCH=0 switches it off)
 };
 
 // STAGES = 4: two CTAs per SM (grids larger than the machine, short K).  STAGES = 8: one CTA per SM with twice the
@@ -150,6 +152,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // ------------------------------ epilogue ------------------------------
     const uint32_t q = warp & 3;  // TMEM lane quadrant this warp may access
     const int m = m0 + q * 32 + lane_id();
+    // epilogue operands on their way while the main loop runs: this row's reference activation (128 B), its arg-max bytes,
+    // the bias slice
+    if (g.prefetch && m < g.M && n0 < g.N) {
+      if (g.ref) prefetch_l1(g.ref + static_cast<size_t>(m) * g.ldd + n0);
+      if (g.epilogue == DTM_EPI_MASK_UNPOOL_BF16) prefetch_l1(g.argmax + (static_cast<size_t>(m) * 49 + (n0 >> 6)) * 64);
+      if (g.bias && lane_id() < 2) prefetch_l1(g.bias + n0 + lane_id() * 32);
+    }
     if (num_kb > 0) {
       mbar_wait(&accum_bar, 0, 3);
       tc_fence_after();
@@ -379,6 +388,10 @@ static int gemm_run(const void* a, int a_mn_major, const void* b, int b_mn_major
   g.seed = seed;
   g.step_ptr = step_ptr;
   g.cluster_reduce = (cluster_reduce && splits == 2) ? 1 : 0;
+  {
+    const char* pe = getenv("DTM_EPI_PREFETCH");
+    g.prefetch = (pe && pe[0] == '0') ? 0 : 1;
+  }
   g.argmax = static_cast<const uint8_t*>(argmax);
   g.planes = static_cast<uint8_t*>(planes);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
