@@ -44,10 +44,8 @@ sys.path.insert(0, ROOT)
 
 # Fallback only (used when the in-run comparison arm could not be measured, e.g. --no-baseline): BASELINE.md section 4,
 # stock PyTorch DDP + NCCL + cuDNN/cuBLAS, same CNN, same box, batch 512/GPU, images/sec.
-BASELINE_MD_IMAGES_PER_SEC = {
-    ("baseline", 1): 483170.0, ("baseline", 2): 677172.0, ("baseline", 4): 1433660.0, ("baseline", 8): 2296187.0,
-    ("reference", 1): 170616.0, ("reference", 2): 342580.0, ("reference", 4): 683660.0,
-    ("wide", 1): 315920.0, ("wide", 2): 571068.0, ("wide", 4): 1125617.0,
+BASELINE_MD_IMAGES_PER_SEC = {      # round 2: best variant (whole step in a CUDA graph, bf16 autocast, channels_last)
+    ("baseline", 1): 579253.0, ("baseline", 2): 1073680.0, ("baseline", 4): 2128059.0, ("baseline", 8): 4084252.0,
 }
 NVLINK_BYTES_PER_SEC = 900e9      # per GPU and direction (task statement / B200_PROFILING.md)
 
