@@ -148,7 +148,8 @@ class ThreadPlane:
         views = self.all_gather_object(t.cpu() if self.rank == src else None)
         if self.rank != src:
             t.copy_(views[src])
-            torch.cuda.synchronize(t.device)
+            if t.is_cuda:
+                torch.cuda.synchronize(t.device)
         self.shared.barrier.wait()          # the source keeps its tensor alive and unchanged until everybody has copied
 
     def abort(self) -> None:

@@ -547,3 +547,50 @@ def test_inference_helper_result_files(tmp_path):
     assert json.load(open(tmp_path / "o" / "r.json"))["num_samples"] == 2
     doc = ih.writeClassificationResult(str(tmp_path / "v.json"), ["k0", "k1"], probs, ground_truth=[0, 3])
     assert doc["accuracy"] == 0.5 and doc["results"][1]["correct"] is False
+
+
+def test_thread_plane_collectives():
+    """Control plane of the single-process tower mode: threads instead of ranks (parallel/control_plane.py)."""
+    import threading
+
+    from distributed_tensorflow_ibm_mnist_b200.parallel.control_plane import ThreadPlane, as_plane
+
+    planes = ThreadPlane.make(3)
+    out = [None] * 3
+
+    def run(r):
+        p = planes[r]
+        assert as_plane(p) is p and p.same_process and p.world_size == 3
+        a = p.all_gather_object({"rank": r})
+        b = p.broadcast_object("from-2" if r == 2 else None, src=2)
+        t = torch.full((4,), float(r))
+        p.broadcast_tensor(t, 1)
+        p.barrier()
+        out[r] = (a, b, t.tolist(), p.all_true(r >= 0), p.all_true(r > 0), p.any_true(r == 2), p.any_true(False))
+
+    ths = [threading.Thread(target=run, args=(r,)) for r in range(3)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join(timeout=60)
+    for r in range(3):
+        a, b, t, all1, all2, any1, any2 = out[r]
+        assert a == [{"rank": 0}, {"rank": 1}, {"rank": 2}] and b == "from-2" and t == [1.0] * 4
+        assert all1 and not all2 and any1 and not any2
+
+
+def test_dist_plane_passes_file_descriptors(tmp_path):
+    """How GPU allocation handles travel between worker processes: SCM_RIGHTS over abstract unix sockets, rendezvous over the
+    process group (gloo here)."""
+    import socket as _s
+    import subprocess
+
+    with _s.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    worker = os.path.join(ROOT, "tests", "helpers", "fd_exchange_worker.py")
+    procs = [subprocess.Popen([sys.executable, worker, str(r), "2", str(port), str(tmp_path)], stdout=subprocess.PIPE,
+                              stderr=subprocess.PIPE, text=True, env=dict(os.environ, PYTHONPATH=ROOT)) for r in range(2)]
+    outs = [p.communicate(timeout=180) for p in procs]
+    for r, (p, (o, e)) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0 and f"FD_EXCHANGE_OK {r}" in o, e[-2000:]
