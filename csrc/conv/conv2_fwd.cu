@@ -34,8 +34,10 @@ constexpr float LRN2_BETA = 0.75f;
 // Epilogue width: the pooling/arg-max code is a long dependent chain (3 shuffles + compares per channel), and with one
 // epilogue warp per scheduler it, not the tensor core, set the kernel time (ncu: tensor pipe 24 % active).  Without
 // LRN the 64 channels split cleanly, so two warps share each TMEM lane quadrant (32 channels each, 8 epilogue warps);
-// LRN needs a pixel's whole channel vector in one thread and keeps the 4-warp layout.
-template <bool LRN> struct C2Epi { static constexpr int WARPS = LRN ? 4 : 8; static constexpr int CH = LRN ? 64 : 32; };
+// With LRN a warp still owns 32 output channels: it also reads the four channels beyond its half from TMEM (the +-4-channel
+// window), so the 8-warp layout holds there too (round 1 kept LRN on four warps with 64 channels per thread: 54.6 us against
+// 21.3 us without LRN).
+template <bool LRN> struct C2Epi { static constexpr int WARPS = 8; static constexpr int CH = 32; };
 
 template <bool LRN>
 __global__ void __launch_bounds__(128 + 32 * C2Epi<LRN>::WARPS, 1)
@@ -152,7 +154,7 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
     // ---- epilogue ------------------------------------------------------------------------------
     constexpr int CH = C2Epi<LRN>::CH;     // channels handled by this warp
     const uint32_t q = warp & 3;           // TMEM lane quadrant
-    const int c0 = LRN ? 0 : static_cast<int>((warp - 4) >> 2) * 32;   // first channel of this warp
+    const int c0 = static_cast<int>((warp - 4) >> 2) * 32;   // first channel of this warp
     const int w_px = lane & 15;            // column inside the 16-wide grid
     const int h_sub = lane >> 4;           // 0/1: row inside the warp's row pair
     int it = 0;
@@ -181,26 +183,37 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
 #pragma unroll
           for (int j = 0; j < CH; ++j) v[j] = __bfloat162float(__float2bfloat16(v[j]));
           if (pixel_valid) {
-            uint4* dst = reinterpret_cast<uint4*>(act2 + (static_cast<size_t>(img) * (IMG * IMG) + h * IMG + w_px) * C2_OUT);
+            uint4* dst = reinterpret_cast<uint4*>(act2 + (static_cast<size_t>(img) * (IMG * IMG) + h * IMG + w_px) * C2_OUT + c0);
 #pragma unroll
             for (int j = 0; j < CH; j += 8)
               dst[j >> 3] = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
                                        pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
           }
-          float sq[CH];
+          // squares of this warp's 32 channels with the 4 channels on either side (zero outside 0..63): the lower half reads
+          // channels 32..35 from the accumulator as well, the upper half 28..31
+          float ext[CH + 8];
+          {
+            uint32_t hr[16];
+            tmem_ld_x16(tmem_base + ((q * 32u) << 16) + a * 64 + (c0 == 0 ? 32 : 16), hr);
+            tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < CH; ++j) sq[j] = v[j] * v[j];
-          float y[CH];
+            for (int k = 0; k < 4; ++k) {
+              const float lo = fmaxf(__uint_as_float(hr[k]) + s_bias[32 + k], 0.0f);         // channels 32..35
+              const float hi = fmaxf(__uint_as_float(hr[12 + k]) + s_bias[28 + k], 0.0f);    // channels 28..31
+              const float lo_r = __bfloat162float(__float2bfloat16(lo)), hi_r = __bfloat162float(__float2bfloat16(hi));
+              ext[k] = c0 == 0 ? 0.0f : hi_r * hi_r;
+              ext[CH + 4 + k] = c0 == 0 ? lo_r * lo_r : 0.0f;
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < CH; ++j) ext[4 + j] = v[j] * v[j];
 #pragma unroll
           for (int j = 0; j < CH; ++j) {
             float sum = 0.0f;
 #pragma unroll
-            for (int d = -4; d <= 4; ++d)
-              if (j + d >= 0 && j + d < CH) sum += sq[j + d];
-            y[j] = v[j] * __powf(LRN2_BIAS + LRN2_ALPHA * sum, -LRN2_BETA);
+            for (int d = 0; d < 9; ++d) sum += ext[j + d];
+            v[j] *= __powf(LRN2_BIAS + LRN2_ALPHA * sum, -LRN2_BETA);
           }
-#pragma unroll
-          for (int j = 0; j < CH; ++j) v[j] = y[j];
         }
         // 2x2 max-pool across lanes l, l^1 (w+1), l^16 (h+1), l^17
         __nv_bfloat16* p2_dst = p2 + (static_cast<size_t>(img) * 49 + ph * 7 + pw) * C2_OUT + c0;
@@ -259,7 +272,7 @@ extern "C" int dtm_conv2_fwd(const void* p1_planes, const void* w2_bf16, const v
   }
   const int grid = min(2 * batch, device_sm_count());
   auto args = [&](auto kern) -> int {
-    DTM_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(lrn ? 256 : 384), C2_SMEM, s, static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
+    DTM_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(384), C2_SMEM, s, static_cast<const uint8_t*>(p1_planes), static_cast<const __nv_bfloat16*>(w2_bf16),
                                     static_cast<const uint8_t*>(packed), bias, batch, static_cast<__nv_bfloat16*>(p2), static_cast<uint8_t*>(argmax),
                                     static_cast<__nv_bfloat16*>(act2), pdl_mode() == 2 ? 1 : 0));
     return 0;
