@@ -1,7 +1,7 @@
 // Both convolution weight gradients of the MNIST CNN in ONE tcgen05 kernel (autodiff of mnist_input.py:142-147 and :161):
 //
 //   dW2[kh][kw][ci][co] = sum_{image, pixel} P1[pixel + tap][ci] * dZ2[pixel][co]          (conv2, exactly conv2_wgrad.cu)
-//   dW1[kh][kw][0][co]  = sum_{image, pixel} X[pixel + tap]      * dZ1[pixel][co]          (conv1, C_in = 1)
+//   dW1[kh][kw][ci][co] = sum_{image, pixel} X[pixel + tap][ci]  * dZ1[pixel][co]          (conv1, C_in = 1 or 3)
 //   db1[co]             = sum_{image, pixel} dZ1[pixel][co]
 //
 // Why one kernel: in round 1 the conv1 gradient ran as a CUDA-core kernel beside conv2_wgrad (one LDS + one FFMA per
@@ -46,7 +46,8 @@ constexpr int FW_Z1_PLANE = FW_ROWS * FW_PITCH * 16;       // 14336
 constexpr int FW_Z1_BYTES = (FW_C1 / 8) * FW_Z1_PLANE;     // 57344
 constexpr int FW_XP_PITCH = 40;                            // bf16 halo image: 32 rows x 40 columns (column w + 7 <= 38)
 constexpr int FW_XP_BYTES = 32 * FW_XP_PITCH * 2;          // 2560
-constexpr int FW_SMEM = FW_STAGES * FW_STAGE_BYTES + FW_E_BYTES + FW_Z1_BYTES + FW_XP_BYTES + 128;
+// C_in image channels: one entry array, one halo image and one accumulator each (C_in = 3: 225 408 bytes, 3 x 32 + 13 x 32 = 512 TMEM columns)
+constexpr int fw_smem(int cin) { return FW_STAGES * FW_STAGE_BYTES + cin * FW_E_BYTES + FW_Z1_BYTES + cin * FW_XP_BYTES + 128; }
 constexpr int FW_BUILDERS = 192;                           // warps 2..7
 constexpr int FW_C1_STEPS = FW_ROWS * FW_PITCH / 16;       // 56 MMAs per conv1 image
 
@@ -72,6 +73,7 @@ DTM_DEVICE void fw_issue_conv2(uint32_t tmem_base, const UmmaDescBase& dz_base, 
   }
 }
 
+template <int CIN>
 __global__ void __launch_bounds__(256, 1)
 conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __restrict__ dz2_planes,
                         const uint8_t* __restrict__ x_u8, const __nv_bfloat16* __restrict__ grad_pooled,
@@ -81,9 +83,9 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
   __shared__ uint64_t full_bar[FW_STAGES], empty_bar[FW_STAGES], done_bar, c1_full, c1_empty;
   __shared__ uint32_t tmem_slot;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
-  uint8_t* s_e = smem + FW_STAGES * FW_STAGE_BYTES;       // image entries E[row][pixel][8 shifts]
-  uint8_t* s_z1 = s_e + FW_E_BYTES;                       // un-pooled conv1 gradient, 4 planes
-  __nv_bfloat16* s_xp = reinterpret_cast<__nv_bfloat16*>(s_z1 + FW_Z1_BYTES);   // halo image, bf16
+  uint8_t* s_e = smem + FW_STAGES * FW_STAGE_BYTES;       // image entries E[ci][row][pixel][8 shifts]
+  uint8_t* s_z1 = s_e + CIN * FW_E_BYTES;                       // un-pooled conv1 gradient, 4 planes
+  __nv_bfloat16* s_xp = reinterpret_cast<__nv_bfloat16*>(s_z1 + FW_Z1_BYTES);   // halo images [ci][32][40], bf16
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
@@ -115,10 +117,10 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
     }
     // conv1 side: gradient planes (their padding pixels stay zero for good), halo image, and the entry rows that never
     // change - rows 0,1 and 30..34 pair with halo rows (zero image) and only carry the bias-gradient 1.0 in slot 5
-    for (int i = threadIdx.x * 16; i < FW_Z1_BYTES + FW_XP_BYTES; i += blockDim.x * 16) *reinterpret_cast<uint4*>(s_z1 + i) = z;
+    for (int i = threadIdx.x * 16; i < FW_Z1_BYTES + CIN * FW_XP_BYTES; i += blockDim.x * 16) *reinterpret_cast<uint4*>(s_z1 + i) = z;
     const uint4 ones = make_uint4(0, 0, 0x3F800000u, 0);       // slot 5 = bf16 1.0
-    for (int i = threadIdx.x; i < FW_E_ROWS * FW_PITCH; i += blockDim.x) {
-      const int rr = i / FW_PITCH;
+    for (int i = threadIdx.x; i < CIN * FW_E_ROWS * FW_PITCH; i += blockDim.x) {
+      const int rr = (i / FW_PITCH) % FW_E_ROWS;
       if (rr < 2 || rr >= 30) *reinterpret_cast<uint4*>(s_e + i * 16) = ones;
     }
   }
@@ -148,7 +150,9 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
     // ------------------------------ MMA issuer ------------------------------
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(64, FW_CI, true, true);
-      const UmmaDescBase e_base = umma_desc_base(smem_u32(s_e), 128, FW_PITCH * 16, UMMA_SWIZZLE_NONE);
+      UmmaDescBase e_base[CIN];
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci) e_base[ci] = umma_desc_base(smem_u32(s_e + ci * FW_E_BYTES), 128, FW_PITCH * 16, UMMA_SWIZZLE_NONE);
       const UmmaDescBase z1_base = umma_desc_base(smem_u32(s_z1), 128, FW_Z1_PLANE, UMMA_SWIZZLE_NONE);
       const uint32_t tmem_c1 = tmem_base + ntaps * FW_CI;
       int it = 0, j = 0;
@@ -166,11 +170,15 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
           mbar_wait(&c1_full, j & 1, 33);
           tc_fence_after();
           if (!(conv1_on & 2)) {
-          if (j == 0) umma_f16_c<false>(tmem_c1, umma_desc_at(e_base, 0), umma_desc_at(z1_base, 0), idesc);
-          else        umma_f16_c<true>(tmem_c1, umma_desc_at(e_base, 0), umma_desc_at(z1_base, 0), idesc);
+#pragma unroll
+            for (int ci = 0; ci < CIN; ++ci) {
+              const uint32_t acc = tmem_c1 + ci * FW_C1;
+              if (j == 0) umma_f16_c<false>(acc, umma_desc_at(e_base[ci], 0), umma_desc_at(z1_base, 0), idesc);
+              else        umma_f16_c<true>(acc, umma_desc_at(e_base[ci], 0), umma_desc_at(z1_base, 0), idesc);
 #pragma unroll 5
-          for (int i = 1; i < FW_C1_STEPS; ++i)
-            umma_f16_c<true>(tmem_c1, umma_desc_at(e_base, i * 256), umma_desc_at(z1_base, i * 256), idesc);
+              for (int i = 1; i < FW_C1_STEPS; ++i)
+                umma_f16_c<true>(acc, umma_desc_at(e_base[ci], i * 256), umma_desc_at(z1_base, i * 256), idesc);
+            }
           }
           umma_commit(&c1_empty);
           ++j;
@@ -185,10 +193,15 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
     for (int img = first; img < batch; img += stride, ++it) {
       if (!conv1_on || (it & 1) == y) continue;
       // global loads of this image first: they are in flight while the previous conv1 image's MMAs are awaited
-      const uint8_t* xs = x_u8 + static_cast<size_t>(img) * 784;
-      uint32_t xw[2] = {0, 0};
-      if (bt < 196) xw[0] = *reinterpret_cast<const uint32_t*>(xs + bt * 4);     // 196 words = 784 bytes (bt < 192 here)
-      if (bt < 4) xw[1] = *reinterpret_cast<const uint32_t*>(xs + (192 + bt) * 4);
+      constexpr int XWORDS = CIN * 196;                            // 784 * C_in bytes, pixels interleaved (HWC)
+      constexpr int NXW = (XWORDS + FW_BUILDERS - 1) / FW_BUILDERS;
+      const uint8_t* xs = x_u8 + static_cast<size_t>(img) * (784 * CIN);
+      uint32_t xw[NXW];
+#pragma unroll
+      for (int k = 0; k < NXW; ++k) {
+        const int wd = bt + k * FW_BUILDERS;
+        xw[k] = wd < XWORDS ? *reinterpret_cast<const uint32_t*>(xs + wd * 4) : 0u;
+      }
       const __nv_bfloat16* gs = grad_pooled + static_cast<size_t>(img) * (IMG * IMG) * FW_C1;
       const uint8_t* as = argmax + static_cast<size_t>(img) * (IMG * IMG) * FW_C1;
       uint4 gv[5];
@@ -204,23 +217,25 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
       }
       mbar_wait_warp(&c1_empty, (j & 1) ^ 1, 34);
       if (conv1_on & 4) { fence_proxy_async_smem(); __syncwarp(); if (lane == 0) mbar_arrive(&c1_full); ++j; continue; }
-      // 1. halo image in bf16: Xp[r + 2][c + 2] = x[r][c] / 255 - 0.5
-      {
-        auto put4 = [&](int word, uint32_t v) {
+      // 1. halo images in bf16: Xp[ci][r + 2][c + 2] = x[r][c][ci] / 255 - 0.5
+#pragma unroll
+      for (int k = 0; k < NXW; ++k) {
+        const int wd = bt + k * FW_BUILDERS;
+        if (wd < XWORDS) {
 #pragma unroll
           for (int b = 0; b < 4; ++b) {
-            const int px = word * 4 + b, r = px / 28, c = px - r * 28;
-            s_xp[(r + 2) * FW_XP_PITCH + c + 2] = __float2bfloat16(static_cast<float>((v >> (8 * b)) & 0xFF) * (1.0f / 255.0f) - 0.5f);
+            const int idx = wd * 4 + b, px = idx / CIN, ci = idx - px * CIN, r = px / 28, c = px - r * 28;
+            s_xp[(ci * 32 + r + 2) * FW_XP_PITCH + c + 2] =
+                __float2bfloat16(static_cast<float>((xw[k] >> (8 * b)) & 0xFF) * (1.0f / 255.0f) - 0.5f);
           }
-        };
-        put4(bt, xw[0]);
-        if (bt < 4) put4(192 + bt, xw[1]);
+        }
       }
       asm volatile("bar.sync 1, 192;" ::: "memory");
       // 2. entries of rows 2..29: E[rr][w][s] = Xp[rr][w + s], slot 5 := 1.0
-      for (int e = bt; e < 28 * FW_PITCH; e += FW_BUILDERS) {
-        const int rr = 2 + e / FW_PITCH, w = e % FW_PITCH;
-        const uint32_t* row = reinterpret_cast<const uint32_t*>(s_xp + rr * FW_XP_PITCH) + (w >> 1);
+      for (int e = bt; e < CIN * 28 * FW_PITCH; e += FW_BUILDERS) {
+        const int ci = e / (28 * FW_PITCH), er = e - ci * (28 * FW_PITCH);
+        const int rr = 2 + er / FW_PITCH, w = er % FW_PITCH;
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(s_xp + (ci * 32 + rr) * FW_XP_PITCH) + (w >> 1);
         uint32_t r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3];
         if (w & 1) {
           const uint32_t r4 = row[4];
@@ -228,7 +243,7 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
           r2 = __funnelshift_r(r2, r3, 16); r3 = __funnelshift_r(r3, r4, 16);
         }
         r2 = (r2 & 0x0000FFFFu) | 0x3F800000u;
-        *reinterpret_cast<uint4*>(s_e + (rr * FW_PITCH + w) * 16) = make_uint4(r0, r1, r2, r3);
+        *reinterpret_cast<uint4*>(s_e + ci * FW_E_BYTES + (rr * FW_PITCH + w) * 16) = make_uint4(r0, r1, r2, r3);
       }
       // 3. un-pooled gradient: pooled pixel (ph, pw), channel group cg -> its four window positions
 #pragma unroll
@@ -280,20 +295,27 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
         // red.add instruction touch 16 different cache lines, and all CTAs of the grid add into the same 26 lines - the L2
         // serialises ~4.5 K requests per line (measured: +10 us).  Transposed through shared memory a warp adds one tap row
         // as a single 128-byte request: 26 requests per CTA.
-        uint32_t r[32];
-        tmem_ld_x32(tmem_base + ((q * 32u) << 16) + ntaps * FW_CI, r);
-        tmem_ld_wait();
-        float* s_red = reinterpret_cast<float*>(s_e);     // [64][33]; the entry buffer is idle once done_bar has fired
-        if (lane < 16) {
+        float* s_red = reinterpret_cast<float*>(s_e);     // [ci][64][33]; the entry buffers are idle once done_bar has fired
 #pragma unroll
-          for (int c = 0; c < FW_C1; ++c) s_red[row * 33 + c] = __uint_as_float(r[c]);
+        for (int ci = 0; ci < CIN; ++ci) {
+          uint32_t r[32];
+          tmem_ld_x32(tmem_base + ((q * 32u) << 16) + ntaps * FW_CI + ci * FW_C1, r);
+          tmem_ld_wait();
+          if (lane < 16) {
+#pragma unroll
+            for (int c = 0; c < FW_C1; ++c) s_red[(ci * 64 + row) * 33 + c] = __uint_as_float(r[c]);
+          }
         }
         asm volatile("bar.sync 2, 128;" ::: "memory");
         for (int m = q; m < 64; m += 4) {
           const int kh = m >> 3, kw = m & 7;
-          const float v = s_red[m * 33 + lane];
-          if (kh < 5 && kw < 5) red_add_f32(dw1 + (kh * 5 + kw) * FW_C1 + lane, v);
-          else if (m == 5)      red_add_f32(db1 + lane, v);
+          if (kh < 5 && kw < 5) {
+#pragma unroll
+            for (int ci = 0; ci < CIN; ++ci)      // TF layout [kh][kw][ci][co]
+              red_add_f32(dw1 + ((kh * 5 + kw) * CIN + ci) * FW_C1 + lane, s_red[(ci * 64 + m) * 33 + lane]);
+          } else if (m == 5) {
+            red_add_f32(db1 + lane, s_red[m * 33 + lane]);       // the all-ones tap of channel 0: sum of the gradient
+          }
         }
       }
     }
@@ -306,28 +328,35 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
 
 }  // namespace dtm
 
-extern "C" int dtm_conv_wgrad_fused(const void* p1_planes, const void* dz2_planes, const void* x_u8, const void* grad_pooled,
+extern "C" int dtm_conv_wgrad_fused(const void* p1_planes, const void* dz2_planes, const void* x_u8, int channels, const void* grad_pooled,
                                     const void* argmax, int batch, float* dw2, float* dw1, float* db1, void* stream) {
   using namespace dtm;
   if (batch <= 0) return dtm_fail("conv_wgrad_fused: batch must be positive");
+  if (channels != 1 && channels != 3) return dtm_fail("conv_wgrad_fused: channels must be 1 or 3");
   if (!p1_planes || !dz2_planes || !x_u8 || !grad_pooled || !argmax || !dw2 || !dw1 || !db1)
     return dtm_fail("conv_wgrad_fused: null argument");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // experiment switch (tools/kernel_bench.py): DTM_FW_NO_CONV1=1 leaves the conv1 part out (dw1 / db1 stay untouched)
-  const char* e = getenv("DTM_FW_NO_CONV1");
   // (values 3 / 5 / 7: conv1 pipeline without its MMAs / without the operand building / without both - timing only)
+  const char* e = getenv("DTM_FW_NO_CONV1");
   const int conv1_on = e ? ((e[0] == '1') ? 0 : atoi(e)) : 1;
   static bool configured[64] = {};     // per device: function attributes belong to a device's context
   const int dev_slot = device_slot();
   if (!configured[dev_slot]) {
-    DTM_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FW_SMEM));
+    DTM_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, fw_smem(1)));
+    DTM_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_fused_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, fw_smem(3)));
     configured[dev_slot] = true;
   }
   const int gx = min(batch, max(1, device_sm_count() / 2));
-  DTM_CUDA_OK(launch_pdl(conv_wgrad_fused_kernel, dim3(gx, 2), dim3(256), FW_SMEM, s, static_cast<const uint8_t*>(p1_planes),
-                         static_cast<const uint8_t*>(dz2_planes), static_cast<const uint8_t*>(x_u8),
-                         static_cast<const __nv_bfloat16*>(grad_pooled), static_cast<const uint8_t*>(argmax), batch, dw2, dw1, db1,
-                         conv1_on));
+  const uint8_t* p1 = static_cast<const uint8_t*>(p1_planes);
+  const uint8_t* dz = static_cast<const uint8_t*>(dz2_planes);
+  const uint8_t* x = static_cast<const uint8_t*>(x_u8);
+  const __nv_bfloat16* gp = static_cast<const __nv_bfloat16*>(grad_pooled);
+  const uint8_t* am = static_cast<const uint8_t*>(argmax);
+  if (channels == 1)
+    DTM_CUDA_OK(launch_pdl(conv_wgrad_fused_kernel<1>, dim3(gx, 2), dim3(256), fw_smem(1), s, p1, dz, x, gp, am, batch, dw2, dw1, db1, conv1_on));
+  else
+    DTM_CUDA_OK(launch_pdl(conv_wgrad_fused_kernel<3>, dim3(gx, 2), dim3(256), fw_smem(3), s, p1, dz, x, gp, am, batch, dw2, dw1, db1, conv1_on));
   DTM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -24,7 +24,7 @@ _lib.register("dtm_conv2_fwd", [P, P, P, P, I, I, P, P, P, P])
 _lib.register("dtm_conv2_dgrad", [P, P, P, P, P, I, I, P, P])
 _lib.register("dtm_conv2_pack_weights", [P, P, P, P])
 _lib.register("dtm_conv2_wgrad", [P, P, I, P, P])
-_lib.register("dtm_conv_wgrad_fused", [P, P, P, P, P, I, P, P, P, P])
+_lib.register("dtm_conv_wgrad_fused", [P, P, P, I, P, P, I, P, P, P, P])
 _lib.register("dtm_unpool2", [P, P, P, I, I, P, P, P])
 _lib.register("dtm_colsum_bf16", [P, I, I, P, P])
 _lib.register("dtm_set_pdl_mode", [I])
@@ -124,11 +124,11 @@ def conv2_wgrad(p1_planes, dz2_planes, dw2, *, batch):
     check(_L().dtm_conv2_wgrad(ptr(p1_planes), ptr(dz2_planes), batch, ptr(dw2), current_stream()), "conv2_wgrad")
 
 
-def conv_wgrad_fused(p1_planes, dz2_planes, x_u8, grad_pooled, argmax, dw2, dw1, db1, *, batch):
-    """conv2 and conv1 (C_in = 1, uint8 input) weight gradients in one tcgen05 kernel (``dtm_conv_wgrad_fused``)."""
+def conv_wgrad_fused(p1_planes, dz2_planes, x_u8, grad_pooled, argmax, dw2, dw1, db1, *, batch, channels=1):
+    """conv2 and conv1 (uint8 input, 1 or 3 channels) weight gradients in one tcgen05 kernel (``dtm_conv_wgrad_fused``)."""
     if x_u8.dtype != torch.uint8:
         raise TypeError("conv_wgrad_fused: uint8 pixels only (use conv1_wgrad + conv2_wgrad for float input)")
-    check(_L().dtm_conv_wgrad_fused(ptr(p1_planes), ptr(dz2_planes), ptr(x_u8), ptr(grad_pooled), ptr(argmax), int(batch),
+    check(_L().dtm_conv_wgrad_fused(ptr(p1_planes), ptr(dz2_planes), ptr(x_u8), int(channels), ptr(grad_pooled), ptr(argmax), int(batch),
                                     ptr(dw2), ptr(dw1), ptr(db1), current_stream()), "conv_wgrad_fused")
 
 

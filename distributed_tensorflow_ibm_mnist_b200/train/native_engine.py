@@ -125,7 +125,7 @@ class NativeEngine:
         # one tcgen05 kernel for both convolution weight gradients (conv1's operands are built by the warps that idle in
         # conv2_wgrad): single-channel uint8 input only; DTM_WGRAD_FUSED=0 restores the two separate kernels.  Pays off
         # together with the persisting-L2 optimizer state (profiles/ab_wgrad_update_r2.md): 152.6 vs 157.6 us per step
-        self._fused_wgrad = spec.channels == 1 and env.get("DTM_WGRAD_FUSED", "1") != "0"
+        self._fused_wgrad = env.get("DTM_WGRAD_FUSED", "1") != "0"
         # experiment switches (tools/ablate.py): kernels to leave out of the step (timing only - results are then wrong) and
         # a flag that puts every kernel on the main stream
         self._skip = set(filter(None, env.get("DTM_SKIP", "").split(",")))
@@ -390,7 +390,7 @@ class NativeEngine:
         fused_wgrad = self._fused_wgrad and x.dtype == torch.uint8 and self._on("conv2_wgrad") and self._on("conv1_wgrad")
         if fused_wgrad:
             native.conv_wgrad_fused(self.p1, self.dz2, x, self.dpool1, self.arg1, self._g("conv2/weights"),
-                                    self._g("conv1/weights"), self._g("conv1/biases"), batch=B); n += 1
+                                    self._g("conv1/weights"), self._g("conv1/biases"), batch=B, channels=s.channels); n += 1
         else:
             # conv2_wgrad is the longer of the two weight-gradient kernels: it stays on the main stream (programmatic edge
             # from dgrad, no cross-stream hand-off on the critical path); conv1_wgrad (26 KB of smem, CUDA cores) co-resides

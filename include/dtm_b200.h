@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define DTM_ABI_VERSION 9
+#define DTM_ABI_VERSION 10
 
 /* GEMM epilogues */
 #define DTM_EPI_STORE_F32 0      /* D(fp32)  = alpha * acc          (split-K: red.add into pre-zeroed D) */
@@ -168,11 +168,11 @@ int dtm_conv2_dgrad(const void* dz2_planes, const void* w2_bf16, const void* pac
                     const void* pool_raw, int batch, int lrn, void* dpool1, void* stream);
 /* dw2 fp32 [5][5][32][64], accumulated (red.add): zero on entry. */
 int dtm_conv2_wgrad(const void* p1_planes, const void* dz2_planes, int batch, float* dw2, void* stream);
-/* dtm_conv2_wgrad and dtm_conv1_wgrad (C_in = 1, uint8 pixels) in ONE tcgen05 kernel: the warps that idle in conv2_wgrad
+/* dtm_conv2_wgrad and dtm_conv1_wgrad (uint8 pixels, channels = 1 or 3) in ONE tcgen05 kernel: the warps that idle in conv2_wgrad
  * build conv1's operands (16-byte shifted-window entries of the image, un-pooled gradient planes) and the MMA warp
  * accumulates dW1 / db1 in spare TMEM columns (autodiff of mnist_input.py:142-147, :161).  Same contracts: dw2, dw1, db1
  * are accumulated with red.add and must be zero on entry; pixels are rounded to bf16 after normalisation. */
-int dtm_conv_wgrad_fused(const void* p1_planes, const void* dz2_planes, const void* x_u8, const void* grad_pooled,
+int dtm_conv_wgrad_fused(const void* p1_planes, const void* dz2_planes, const void* x_u8, int channels, const void* grad_pooled,
                          const void* argmax, int batch, float* dw2, float* dw1, float* db1, void* stream);
 /* dp2 bf16 [B][49][64] -> dz2_planes (every byte of the valid region is written) ; db2[64] accumulated. */
 int dtm_unpool2(const void* dp2, const void* argmax, const void* act2, int batch, int lrn, void* dz2_planes, float* db2,

@@ -297,8 +297,8 @@ def test_conv1_wgrad(B, C, tc):
     assert _rel_err(db.cpu(), dz.sum(dim=(0, 2, 3))) < 1e-4
 
 
-@pytest.mark.parametrize("B", [37, 148, 600])
-def test_conv_wgrad_fused(B):
+@pytest.mark.parametrize("B,C", [(37, 1), (148, 1), (600, 1), (37, 3), (300, 3)])
+def test_conv_wgrad_fused(B, C):
     """Both convolution weight gradients from ONE tcgen05 kernel (conv_wgrad_fused.cu) against fp32 autograd of the two
     convolutions.  37 images: one image per CTA, every conv1 image on the 12-tap half; 148: two iterations (both halves do
     conv1 work); 600: several images per CTA, the accumulators run across the double-buffered operand sets."""
@@ -311,7 +311,7 @@ def test_conv_wgrad_fused(B):
     F.conv2d(p1.permute(0, 3, 1, 2), w2, None, padding=2).backward(dz2.permute(0, 3, 1, 2))
     want_dw2 = w2.grad.permute(2, 3, 1, 0)
     # conv1 side
-    x = torch.randint(0, 256, (B, 784), dtype=torch.uint8, generator=g)
+    x = torch.randint(0, 256, (B, 784 * C), dtype=torch.uint8, generator=g)
     gp = _bf(torch.randn(B, 196, 32, generator=g) * (torch.rand(B, 196, 32, generator=g) > 0.5))
     arg = torch.randint(0, 4, (B, 196, 32), dtype=torch.uint8, generator=g)
     dz1 = torch.zeros(B, 14, 2, 14, 2, 32)
@@ -319,15 +319,15 @@ def test_conv_wgrad_fused(B):
     for d in range(4):
         dz1[:, :, d >> 1, :, d & 1, :] = torch.where(a == d, gp.view(B, 14, 14, 32), torch.zeros(()))
     dz1 = dz1.view(B, 28, 28, 32).permute(0, 3, 1, 2)
-    xin = _bf(x.float() * (1.0 / 255) - 0.5).view(B, 28, 28, 1).permute(0, 3, 1, 2)
-    w1 = torch.zeros(32, 1, 5, 5, requires_grad=True)
+    xin = _bf(x.float() * (1.0 / 255) - 0.5).view(B, 28, 28, C).permute(0, 3, 1, 2)
+    w1 = torch.zeros(32, C, 5, 5, requires_grad=True)
     F.conv2d(xin, w1, None, padding=2).backward(dz1)
 
     dw2 = torch.zeros(5, 5, 32, 64, device=DEV)
-    dw1 = torch.zeros(5, 5, 1, 32, device=DEV)
+    dw1 = torch.zeros(5, 5, C, 32, device=DEV)
     db1 = torch.zeros(32, device=DEV)
     native.conv_wgrad_fused(layouts.nhwc_to_planes(p1.to(DEV)), layouts.nhwc_to_planes(dz2.to(DEV)),
-                            x.to(DEV), gp.to(torch.bfloat16).to(DEV), arg.to(DEV), dw2, dw1, db1, batch=B)
+                            x.to(DEV), gp.to(torch.bfloat16).to(DEV), arg.to(DEV), dw2, dw1, db1, batch=B, channels=C)
     torch.cuda.synchronize()
     assert _rel_err(dw2.cpu(), want_dw2) < 1e-3
     assert _rel_err(dw1.cpu(), w1.grad.permute(2, 3, 1, 0)) < 1e-4

@@ -82,9 +82,9 @@ def main() -> int:
     if not s.lrn:
         cases["dP2_unpool"] = lambda: native.gemm_mask_unpool(eng.dh_last, f.weight_bf16("local3/weights"), eng.p2, eng.arg2, eng.dp2, eng.dz2,
                                                               batch=B, hidden=s.fc1)
-    if s.channels == 1:
+    if True:
         fused = lambda: native.conv_wgrad_fused(eng.p1, eng.dz2, xs, eng.dpool1, eng.arg1, f.gradient("conv2/weights"),
-                                                f.gradient("conv1/weights"), f.gradient("conv1/biases"), batch=B)
+                                                f.gradient("conv1/weights"), f.gradient("conv1/biases"), batch=B, channels=s.channels)
         cases["conv_wgrad_fused"] = fused
         cases["conv_wgrad_fused_no_conv1"] = ("env", {"DTM_FW_NO_CONV1": 1}, fused)
         cases["conv_wgrad_fused_no_c1_mma"] = ("env", {"DTM_FW_NO_CONV1": 3}, fused)
