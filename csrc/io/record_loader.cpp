@@ -179,12 +179,24 @@ struct Loader {
   bool first_epoch = true;
   std::mt19937_64 file_rng;
 
+  // A chunk of consecutive raw records (payload + its CRC word each) of ONE file.  Taking records one by one made the
+  // threads hand the reader lock to each other for every 800 bytes (two threads were slower than one); a chunk amortises it.
+  struct Chunk {
+    std::vector<uint8_t> bytes;
+    std::vector<std::pair<size_t, uint64_t>> recs;     // (offset of the payload in `bytes`, payload length)
+    std::string path;
+  };
+  static constexpr int CHUNK_RECORDS = 128;
+
   // false: stop requested or error recorded
-  bool next_record(std::vector<uint8_t>& buf, uint64_t* len_out) {
+  bool next_chunk(Chunk& c) {
     std::lock_guard<std::mutex> rl(read_mu);
+    c.bytes.clear();
+    c.recs.clear();
     for (;;) {
       if (stop.load()) return false;
       if (!cur) {
+        if (!c.recs.empty()) return true;          // a chunk never spans two files
         if (next_file == order.size()) {          // epoch boundary
           if (!first_epoch && epoch_records == 0) { fail("input files contain no records"); return false; }
           first_epoch = false;
@@ -196,7 +208,9 @@ struct Loader {
         cur_path = order[next_file++];
         cur = fopen(cur_path.c_str(), "rb");
         if (!cur) { fail("Failed to find file: " + cur_path); return false; }
+        setvbuf(cur, nullptr, _IOFBF, 1 << 20);
       }
+      c.path = cur_path;
       uint8_t hdr[12];
       const size_t got = fread(hdr, 1, 12, cur);
       if (got == 0) { fclose(cur); cur = nullptr; continue; }     // clean end of file
@@ -208,39 +222,65 @@ struct Loader {
       memcpy(&len_crc, hdr + 8, 4);
       if (masked_crc(hdr, 8) != len_crc) return bad("corrupt TFRecord length in ");
       if (len > (1ull << 30)) return bad("implausible TFRecord length in ");
-      buf.resize(len + 4);
-      if (fread(buf.data(), 1, len + 4, cur) != len + 4) return bad("truncated TFRecord in ");
-      uint32_t data_crc;
-      memcpy(&data_crc, buf.data() + len, 4);
-      if (masked_crc(buf.data(), len) != data_crc) return bad("corrupt TFRecord payload in ");
+      const size_t off = c.bytes.size();
+      c.bytes.resize(off + len + 4);
+      if (fread(c.bytes.data() + off, 1, len + 4, cur) != len + 4) return bad("truncated TFRecord in ");
+      c.recs.emplace_back(off, len);
       ++epoch_records;
-      *len_out = len;
-      return true;
+      if (static_cast<int>(c.recs.size()) >= CHUNK_RECORDS) return true;
     }
   }
 
+  // Shuffle-queue hand-off: the mutex only guards the slot lists; pixels are copied in and out of a slot while nobody else
+  // can name it (a producer owns a slot between taking it off the free list and appending it to `filled`).
   void produce() {
-    std::vector<uint8_t> buf;
-    uint64_t len = 0;
-    while (next_record(buf, &len)) {
-      const uint8_t* img = nullptr;
-      size_t img_len = 0;
-      int64_t label = 0;
-      if (!parse_example(buf.data(), len, &img, &img_len, &label)) { fail("record without image_raw/label features in " + cur_path); return; }
-      if (static_cast<int>(img_len) != image_bytes) {
-        fail("record holds " + std::to_string(img_len) + " image bytes, expected " + std::to_string(image_bytes));
-        return;
+    Chunk c;
+    std::vector<const uint8_t*> imgs;
+    std::vector<int32_t> labs;
+    std::vector<int> slots;
+    while (next_chunk(c)) {
+      imgs.clear();
+      labs.clear();
+      for (const auto& rec : c.recs) {       // payload CRC, Example parsing and validation: outside every lock
+        const uint8_t* payload = c.bytes.data() + rec.first;
+        uint32_t data_crc;
+        memcpy(&data_crc, payload + rec.second, 4);
+        if (masked_crc(payload, rec.second) != data_crc) { fail("corrupt TFRecord payload in " + c.path); return; }
+        const uint8_t* img = nullptr;
+        size_t img_len = 0;
+        int64_t label = 0;
+        if (!parse_example(payload, rec.second, &img, &img_len, &label)) { fail("record without image_raw/label features in " + c.path); return; }
+        if (static_cast<int>(img_len) != image_bytes) {
+          fail("record holds " + std::to_string(img_len) + " image bytes, expected " + std::to_string(image_bytes));
+          return;
+        }
+        imgs.push_back(img);
+        labs.push_back(static_cast<int32_t>(label));
       }
-      std::unique_lock<std::mutex> lk(mu);
-      not_full.wait(lk, [&] { return stop.load() || !free_slots.empty(); });
-      if (stop.load()) return;
-      const int slot = free_slots.back();
-      free_slots.pop_back();
-      memcpy(slab.data() + static_cast<size_t>(slot) * image_bytes, img, image_bytes);
-      labels[slot] = static_cast<int32_t>(label);
-      filled.push_back(slot);
-      ++records_read;
-      if (static_cast<int>(filled.size()) > min_after) enough.notify_one();
+      size_t done = 0;
+      while (done < imgs.size()) {           // as many free slots as there are, at least one, per lock round
+        slots.clear();
+        {
+          std::unique_lock<std::mutex> lk(mu);
+          not_full.wait(lk, [&] { return stop.load() || !free_slots.empty(); });
+          if (stop.load()) return;
+          while (!free_slots.empty() && done + slots.size() < imgs.size()) {
+            slots.push_back(free_slots.back());
+            free_slots.pop_back();
+          }
+        }
+        for (size_t k = 0; k < slots.size(); ++k) {
+          memcpy(slab.data() + static_cast<size_t>(slots[k]) * image_bytes, imgs[done + k], image_bytes);
+          labels[slots[k]] = labs[done + k];
+        }
+        {
+          std::lock_guard<std::mutex> lk(mu);
+          for (int sl : slots) filled.push_back(sl);
+          records_read += slots.size();
+          if (static_cast<int>(filled.size()) > min_after) enough.notify_one();
+        }
+        done += slots.size();
+      }
     }
   }
 
@@ -288,28 +328,39 @@ extern "C" void* dtm_loader_create(const char* const* files, int n_files, int ba
 extern "C" int dtm_loader_next(void* handle, uint8_t* pixels_out, int32_t* labels_out) {
   Loader* L = static_cast<Loader*>(handle);
   if (!L || !pixels_out || !labels_out) return dtm::dtm_fail("loader: null argument");
-  for (int i = 0; i < L->batch; ++i) {
+  // dequeue_many(batch): every element drawn uniformly from the queue while it holds more than min_after_dequeue elements
+  // (slot indices only under the lock), then the pixels are copied out and the slots go back to the free list
+  std::vector<int> picked(L->batch);
+  {
     std::unique_lock<std::mutex> lk(L->mu);
-    L->enough.wait(lk, [&] { return !L->error.empty() || static_cast<int>(L->filled.size()) > L->min_after; });
-    if (!L->error.empty()) {
-      g_loader_error = L->error;
-      return dtm::dtm_fail(g_loader_error.c_str());
+    for (int i = 0; i < L->batch; ++i) {
+      L->enough.wait(lk, [&] { return !L->error.empty() || static_cast<int>(L->filled.size()) > L->min_after; });
+      if (!L->error.empty()) {
+        g_loader_error = L->error;
+        for (int k = 0; k < i; ++k) L->free_slots.push_back(picked[k]);
+        return dtm::dtm_fail(g_loader_error.c_str());
+      }
+      size_t j = 0;
+      if (L->shuffle) j = static_cast<size_t>(L->consumer_rng() % L->filled.size());
+      picked[i] = L->filled[j];
+      if (L->shuffle) {
+        L->filled[j] = L->filled.back();
+        L->filled.pop_back();
+      } else {
+        L->filled.erase(L->filled.begin());
+      }
     }
-    size_t j = 0;
-    if (L->shuffle) j = static_cast<size_t>(L->consumer_rng() % L->filled.size());
-    const int slot = L->filled[j];
-    if (L->shuffle) {
-      L->filled[j] = L->filled.back();
-      L->filled.pop_back();
-    } else {
-      L->filled.erase(L->filled.begin());
-    }
-    memcpy(pixels_out + static_cast<size_t>(i) * L->image_bytes, L->slab.data() + static_cast<size_t>(slot) * L->image_bytes,
-           L->image_bytes);
-    labels_out[i] = L->labels[slot];
-    L->free_slots.push_back(slot);
-    L->not_full.notify_one();
   }
+  for (int i = 0; i < L->batch; ++i) {
+    memcpy(pixels_out + static_cast<size_t>(i) * L->image_bytes, L->slab.data() + static_cast<size_t>(picked[i]) * L->image_bytes,
+           L->image_bytes);
+    labels_out[i] = L->labels[picked[i]];
+  }
+  {
+    std::lock_guard<std::mutex> lk(L->mu);
+    for (int i = 0; i < L->batch; ++i) L->free_slots.push_back(picked[i]);
+  }
+  L->not_full.notify_all();
   return 0;
 }
 

@@ -463,13 +463,17 @@ def test_tfrecord_batches_shuffle_and_validation(tmp_path, native):
         bad.next()
     bad.close()
     # two reader threads share ONE record stream (the reference's single TFRecordReader): nothing of the first epoch is
-    # delivered twice.  250 distinct records (pixel value = record index); the pipeline looks ahead at most capacity +
-    # min_after + batch = 20 + 30 + 20 + 10 records, so the first 160 dequeued records all belong to epoch one
+    # delivered twice.  1200 distinct records (id in the first two pixels); the pipeline looks ahead at most one chunk of 128
+    # records per thread + capacity + min_after + batch = 256 + 50 + 20 + 10 records, so the first 800 dequeued records all
+    # belong to epoch one
     pu = str(tmp_path / "unique.tfrecord")
-    tfrecord.write_mnist_tfrecord(pu, [bytes([i]) * 784 for i in range(250)], [i % 10 for i in range(250)])
+    tfrecord.write_mnist_tfrecord(pu, [bytes([i % 256, i // 256]) + bytes(782) for i in range(1200)], [i % 10 for i in range(1200)])
     once = readers.TFRecordBatches([pu], 10, 784, min_after_dequeue=20, seed=4, num_threads=2, native=native)
-    got = [int(v) for _ in range(16) for v in once.next()[0][:, 0]]
-    assert len(set(got)) == len(got) == 160
+    got = []
+    for _ in range(80):
+        xb = once.next()[0]
+        got += [int(a) + 256 * int(b) for a, b in zip(xb[:, 0], xb[:, 1])]
+    assert len(set(got)) == len(got) == 800
     once.close()
     # unshuffled: file order, every record exactly once per epoch
     seq = readers.TFRecordBatches([p], 50, 784, shuffle=False, native=native)
