@@ -17,6 +17,7 @@
 // the pooled pixel sit in one thread, so LRN (window +-4 channels) stays in registers too.
 //
 // Warp roles: 0-3 epilogue (TMEM lane quadrant = warp index), 4-7 im2col producers, 8 MMA issuer, 9 TMEM allocator.
+#include <stdlib.h>
 #include "../common/ptx.cuh"
 #include "../common/host_util.h"
 #include "../../include/dtm_b200.h"
@@ -255,12 +256,21 @@ conv1_tc_kernel(const void* __restrict__ x, int in_is_float, const float* __rest
 
 }  // namespace dtm
 
+// conv1_sw.cu: the same contract without im2col (default since round 2)
+int dtm_conv1_fwd_shifted_window(const void* x, int in_is_float, int channels, const float* w, const float* bias, int batch, int lrn,
+                                 void* p1_planes, void* argmax, void* pool_raw, void* stream);
+
 extern "C" int dtm_conv1_fwd(const void* x, int in_is_float, int channels, const float* w, const float* bias, int batch,
                              int lrn, void* p1_planes, void* argmax, void* pool_raw, void* stream) {
   using namespace dtm;
   if (channels != 1 && channels != 3) return dtm_fail("conv1_fwd: channels must be 1 or 3");
   if (batch <= 0) return dtm_fail("conv1_fwd: batch must be positive");
   if (lrn && !pool_raw) return dtm_fail("conv1_fwd: LRN needs the pool_raw output buffer");
+  {
+    const char* e = getenv("DTM_CONV1_IM2COL");      // 1 = the round-1 kernel below (explicit im2col tiles), kept as the A/B arm
+    if (!(e && e[0] == '1'))
+      return dtm_conv1_fwd_shifted_window(x, in_is_float, channels, w, bias, batch, lrn, p1_planes, argmax, pool_raw, stream);
+  }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   uint8_t* p = static_cast<uint8_t*>(p1_planes);
   uint8_t* a = static_cast<uint8_t*>(argmax);
