@@ -62,7 +62,7 @@ def main() -> int:
         print("no CUDA kernel records (CUPTI unavailable?)")
         return 1
     # split into steps at every conv1 forward kernel
-    starts = [i for i, r in enumerate(recs) if "conv1_tc_kernel" in r["name"]]
+    starts = [i for i, r in enumerate(recs) if "conv1_tc_kernel" in r["name"] or "conv1_sw_kernel" in r["name"]]
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(recs, open(os.path.join(ROOT, "gpurun_out", "timeline.json"), "w"))
     if len(starts) < 4:
