@@ -110,13 +110,16 @@ def test_gemm_cluster_split_k(M, N, K, b_mn):
 
 
 # ----------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("channels,lrn", [(1, False), (3, True)])
-def test_conv1_forward(channels, lrn):
+@pytest.mark.parametrize("channels,lrn,B,im2col", [(1, False, 37, False), (3, True, 37, False), (1, True, 700, False), (3, False, 330, False),
+                                                     (1, False, 37, True), (3, True, 37, True)])
+def test_conv1_forward(channels, lrn, B, im2col, monkeypatch):
+    """Default kernel (conv1_sw.cu, shifted-window operand) and the round-1 im2col kernel (DTM_CONV1_IM2COL=1).  700 / 330 images:
+    several images per persistent CTA, so the double-buffered entry sets and the accumulator ring wrap."""
     native, layouts = _native()
     from distributed_tensorflow_ibm_mnist_b200.models.oracle import tf_lrn
 
+    monkeypatch.setenv("DTM_CONV1_IM2COL", "1" if im2col else "0")
     g = torch.Generator().manual_seed(11)
-    B = 37
     x = torch.randint(0, 256, (B, 784 * channels), dtype=torch.uint8, generator=g)
     w = torch.randn(5, 5, channels, 32, generator=g) * 0.2
     b = torch.randn(32, generator=g) * 0.1
