@@ -35,7 +35,7 @@ def kernels(B: int, fc1: int = 1024):
     bucket0 = w3 + fc1 + fc1 * 10 + 10
     upd = lambda n: n * (4 * 5 + 4 * 4 + 2)          # read w,g,m,v,ema ; write w,m,v,ema ; write bf16
     return [
-        ("conv1_tc (fwd+pool)", "conv1_tc_kernel", None, 2 * B * px1 * 25 * 32, B * px1 + p1_planes + B * px2 * 32),
+        ("conv1 (fwd+pool)", "conv1_", None, 2 * B * px1 * 25 * 32, B * px1 + p1_planes + B * px2 * 32),
         ("conv2_fwd (+pool)", "conv2_fwd_kernel", None, 2 * B * px2 * 800 * 64, p1_planes + 102400 + B * 49 * 64 * 3),
         ("fc1 GEMM (+bias,ReLU,dropout)", "gemm_bf16_kernel<0, 1, 8>", None, 2 * B * 3136 * fc1, B * 3136 * 2 + w3 * 2 + B * fc1 * 2),
         ("head_forward (+dH)", "head_forward_kernel", None, 2 * 2 * B * fc1 * 10, B * fc1 * 2 * 2 + fc1 * 10 * 4),
