@@ -47,6 +47,7 @@ flags.DEFINE_float("lr_decay", 0.0, "Learning-rate decay factor (0 = parameter m
 flags.DEFINE_string("optimizer", "", "sgd | momentum | adam ('' = parameter manager)")
 flags.DEFINE_string("train_data", "", "Comma-separated TFRecord files for training")
 flags.DEFINE_string("test_data", "", "Comma-separated TFRecord files for the test split")
+flags.DEFINE_integer("input_threads", 2, "Reader threads of the TFRecord input pipeline (mnist_input.py:68 fixes num_threads=2)")
 flags.DEFINE_boolean("use_test_split", False, "Train on the test split, as the reference does (main.py:85)")
 flags.DEFINE_string("engine", "auto", "auto | native (sm_100a kernels) | torch (portable oracle path)")
 flags.DEFINE_string("backend", "", "torch.distributed backend for the control plane ('' = nccl on GPU, gloo on CPU)")
@@ -194,7 +195,8 @@ def train(role=None, plane=None, hp=None):
     if files:
         from distributed_tensorflow_ibm_mnist_b200.data.readers import TFRecordBatches
 
-        source = TFRecordBatches(files, batch_size, spec.image_pixels, seed=hp.seed + role.rank, pin=use_cuda)
+        source = TFRecordBatches(files, batch_size, spec.image_pixels, seed=hp.seed + role.rank, pin=use_cuda,
+                                 num_threads=max(1, FLAGS.input_threads))
         print("image Shape")
         print((spec.image_pixels,))
     else:

@@ -23,6 +23,9 @@ def test_crc32c_known_vectors():
     big = bytes(range(256)) * 41
     assert crc32c.crc32c(big) == crc32c._crc32c_py(big)     # native (when built) == table
     assert crc32c.crc32c(big[100:], crc32c.crc32c(big[:100])) == crc32c.crc32c(big)   # incremental
+    for n in (767, 768, 769, 775, 1535, 1536, 1543, 2304, 2311, 5000):                # around the native path's 3 x 256-byte blocks
+        for off in (0, 1, 7):
+            assert crc32c.crc32c(big[off:off + n], 0x1234) == crc32c._crc32c_py(big[off:off + n], 0x1234), (n, off)
 
 
 def test_crc_mask_roundtrip_and_tensorboard_agreement():

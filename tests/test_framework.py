@@ -500,6 +500,56 @@ def test_tfrecord_batches_shuffle_and_validation(tmp_path, native):
     assert len(got) == n and got[3][2] == 3 and got[0][0].endswith(":0")
 
 
+def test_native_loader_mixed_record_shapes(tmp_path):
+    """The C++ reader's remembered-record-shape fast path must fall back to the general Example parser whenever a record
+    differs from the remembered one anywhere outside its pixels and label value: other feature sets, other field order,
+    labels that need a two-byte varint, un-packed int64 lists.  Every record is checked against the Python codec."""
+    from distributed_tensorflow_ibm_mnist_b200.data import readers
+    from distributed_tensorflow_ibm_mnist_b200.formats import proto, tfrecord
+
+    if readers._native_loader_lib() is None:
+        pytest.skip("libdtm_b200.so not built")
+
+    def bytes_feature(b):
+        return proto.f_bytes(1, proto.f_bytes(1, b))
+
+    def int_feature(v, packed=True):
+        return proto.f_bytes(3, proto.f_bytes(1, proto.enc_varint(v)) if packed else proto.f_varint(1, v))
+
+    def example(entries):
+        return proto.f_bytes(1, b"".join(proto.f_bytes(1, proto.f_str(1, k) + proto.f_bytes(2, f)) for k, f in entries))
+
+    rng = np.random.default_rng(5)
+    recs, want = [], []
+    for i in range(400):
+        img = rng.integers(0, 256, 784, dtype=np.uint8).tobytes()
+        label = [i % 10, 128 + i % 100, 5, 300][i % 4] if i % 7 == 0 else i % 10
+        kind = (i // 5) % 4                                  # runs of five records per structure
+        if kind == 0:
+            e = example([("image_raw", bytes_feature(img)), ("label", int_feature(label))])
+        elif kind == 1:
+            e = example([("label", int_feature(label)), ("image_raw", bytes_feature(img))])
+        elif kind == 2:
+            e = example([("depth", int_feature(1)), ("image_raw", bytes_feature(img)), ("label", int_feature(label, packed=False)),
+                         ("width", int_feature(28))])
+        else:
+            e = tfrecord.mnist_example(img, label)
+        assert tfrecord.decode_example(e)["label"] == label
+        recs.append(e)
+        want.append((img, label))
+    path = str(tmp_path / "mixed.tfrecord")
+    with tfrecord.TFRecordWriter(path) as w:
+        for e in recs:
+            w.write(e)
+    ds = readers.TFRecordBatches([path], 50, 784, shuffle=False, native=True)
+    for b in range(8):
+        x, y = ds.next()
+        for j in range(50):
+            img, label = want[b * 50 + j]
+            assert bytes(x[j].numpy().tobytes()) == img and int(y[j]) == label, (b, j)
+    ds.close()
+
+
 def test_image_preprocessing_helpers():
     from distributed_tensorflow_ibm_mnist_b200.data import readers
 
