@@ -22,6 +22,7 @@
 #include <algorithm>
 #include <atomic>
 #include <condition_variable>
+#include <deque>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -221,8 +222,8 @@ struct Loader {
   // ONE record stream for all reader threads, like the reference's single TFRecordReader behind its filename queue
   // (mnist_input.py:57-71): under `read_mu` a thread only walks the record headers of the current file (length + its CRC,
   // 12 bytes per record) and takes the next CHUNK_RECORDS records as (offset, length) pairs into the file's read-only
-  // mapping; payload CRC, Example parsing and the copy into the shuffle queue run outside every lock, straight from the
-  // page cache - every record is delivered once per epoch, whichever thread asks, and no byte is copied twice.
+  // mapping; payload CRC and Example parsing run outside every lock, straight from the page cache - every record is
+  // delivered once per epoch, whichever thread asks.
   struct Mapping {
     const uint8_t* base = nullptr;
     size_t size = 0;
@@ -379,6 +380,19 @@ struct Loader {
   }
 
   size_t queued() const { return filled.size() - head; }
+
+  // Batch ring (dtm_loader_ring_*): one more thread dequeues whole batches into caller-owned (pinned) buffers ahead of
+  // the trainer, which then only swaps buffer indices.
+  struct Ring {
+    bool running = false;
+    std::vector<uint8_t*> buffers;
+    uint64_t label_offset = 0;
+    std::deque<int> free, ready;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::string error;
+    std::thread worker;
+  } ring;
 };
 
 thread_local std::string g_loader_error;
@@ -414,23 +428,20 @@ extern "C" void* dtm_loader_create(const char* const* files, int n_files, int ba
   return L;
 }
 
-extern "C" int dtm_loader_next(void* handle, uint8_t* pixels_out, int32_t* labels_out) {
-  Loader* L = static_cast<Loader*>(handle);
-  if (!L || !pixels_out || !labels_out) return dtm::dtm_fail("loader: null argument");
-  // dequeue_many(batch): every element drawn uniformly from the queue while it holds more than min_after_dequeue elements
-  // (views only under the lock; their places are free for the producers at once), then the pixels are copied out
+// dequeue_many(batch): every element drawn uniformly from the queue while it holds more than min_after_dequeue elements
+// (views only under the lock; their places are free for the producers at once), then the pixels are copied out.
+// Returns an empty string, or the error that ended the stream.
+static std::string dequeue_batch(Loader* L, uint8_t* pixels_out, int32_t* labels_out) {
   std::vector<Loader::Entry> picked(L->batch);
   {
     std::unique_lock<std::mutex> lk(L->mu);
     for (int i = 0; i < L->batch; ++i) {
       if (static_cast<int>(L->queued()) <= L->min_after) {
         L->not_full.notify_all();                  // about to sleep: the producers may use the places taken so far
-        L->enough.wait(lk, [&] { return !L->error.empty() || static_cast<int>(L->queued()) > L->min_after; });
+        L->enough.wait(lk, [&] { return L->stop.load() || !L->error.empty() || static_cast<int>(L->queued()) > L->min_after; });
       }
-      if (!L->error.empty()) {
-        g_loader_error = L->error;
-        return dtm::dtm_fail(g_loader_error.c_str());
-      }
+      if (!L->error.empty()) return L->error;
+      if (L->stop.load()) return "loader is shutting down";
       if (L->shuffle) {
         const size_t j = static_cast<size_t>(L->consumer_rng() % L->filled.size());
         picked[i] = L->filled[j];
@@ -457,6 +468,82 @@ extern "C" int dtm_loader_next(void* handle, uint8_t* pixels_out, int32_t* label
     memcpy(pixels_out + static_cast<size_t>(i) * ib, picked[i].pixels, ib);
     labels_out[i] = picked[i].label;
   }
+  return std::string();
+}
+
+extern "C" int dtm_loader_next(void* handle, uint8_t* pixels_out, int32_t* labels_out) {
+  Loader* L = static_cast<Loader*>(handle);
+  if (!L || !pixels_out || !labels_out) return dtm::dtm_fail("loader: null argument");
+  if (L->ring.running) return dtm::dtm_fail("loader: dtm_loader_next after dtm_loader_ring_start (the ring's thread owns the queue's consumer side)");
+  g_loader_error = dequeue_batch(L, pixels_out, labels_out);
+  return g_loader_error.empty() ? 0 : dtm::dtm_fail(g_loader_error.c_str());
+}
+
+// ---- batch ring: a thread of the loader assembles whole batches ahead of the trainer ------------------------------------
+extern "C" int dtm_loader_ring_start(void* handle, uint8_t* const* buffers, int n_buffers, uint64_t label_offset) {
+  Loader* L = static_cast<Loader*>(handle);
+  if (!L || !buffers || n_buffers < 2) return dtm::dtm_fail("loader ring: needs a loader and at least two buffers");
+  if (L->ring.running) return dtm::dtm_fail("loader ring: already started");
+  if (label_offset < static_cast<uint64_t>(L->batch) * L->image_bytes || label_offset % 4) {
+    return dtm::dtm_fail("loader ring: labels must follow the pixels at a 4-byte aligned offset");
+  }
+  Loader::Ring& R = L->ring;
+  R.buffers.assign(buffers, buffers + n_buffers);
+  R.label_offset = label_offset;
+  for (int i = 0; i < n_buffers; ++i) R.free.push_back(i);
+  R.running = true;
+  R.worker = std::thread([L] {
+    Loader::Ring& R = L->ring;
+    for (;;) {
+      int idx;
+      {
+        std::unique_lock<std::mutex> lk(R.mu);
+        R.cv.wait(lk, [&] { return L->stop.load() || !R.free.empty(); });
+        if (L->stop.load()) return;
+        idx = R.free.front();
+        R.free.pop_front();
+      }
+      uint8_t* buf = R.buffers[idx];
+      std::string err = dequeue_batch(L, buf, reinterpret_cast<int32_t*>(buf + R.label_offset));
+      std::lock_guard<std::mutex> lk(R.mu);
+      if (!err.empty()) {
+        R.error = err;
+        R.cv.notify_all();
+        return;
+      }
+      R.ready.push_back(idx);
+      R.cv.notify_all();
+    }
+  });
+  return 0;
+}
+
+extern "C" int dtm_loader_ring_acquire(void* handle) {
+  Loader* L = static_cast<Loader*>(handle);
+  if (!L || !L->ring.running) { dtm::dtm_fail("loader ring: not started"); return -1; }
+  Loader::Ring& R = L->ring;
+  std::unique_lock<std::mutex> lk(R.mu);
+  R.cv.wait(lk, [&] { return !R.ready.empty() || !R.error.empty() || L->stop.load(); });
+  if (!R.ready.empty()) {                         // batches assembled before an error are still delivered
+    const int idx = R.ready.front();
+    R.ready.pop_front();
+    return idx;
+  }
+  g_loader_error = R.error.empty() ? "loader is shutting down" : R.error;
+  dtm::dtm_fail(g_loader_error.c_str());
+  return -1;
+}
+
+extern "C" int dtm_loader_ring_release(void* handle, int index) {
+  Loader* L = static_cast<Loader*>(handle);
+  if (!L || !L->ring.running) return dtm::dtm_fail("loader ring: not started");
+  Loader::Ring& R = L->ring;
+  if (index < 0 || index >= static_cast<int>(R.buffers.size())) return dtm::dtm_fail("loader ring: bad buffer index");
+  {
+    std::lock_guard<std::mutex> lk(R.mu);
+    R.free.push_back(index);
+  }
+  R.cv.notify_all();
   return 0;
 }
 
@@ -476,6 +563,11 @@ extern "C" void dtm_loader_destroy(void* handle) {
   }
   L->not_full.notify_all();
   L->enough.notify_all();
+  if (L->ring.running) {
+    { std::lock_guard<std::mutex> lk(L->ring.mu); }
+    L->ring.cv.notify_all();
+    L->ring.worker.join();
+  }
   for (auto& t : L->threads) t.join();
   delete L;
 }

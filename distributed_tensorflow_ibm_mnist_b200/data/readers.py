@@ -50,6 +50,9 @@ def _native_loader_lib():
         from ctypes import c_char_p, c_int, c_uint64, c_void_p, POINTER
         _lib.register("dtm_loader_create", [POINTER(c_char_p), c_int, c_int, c_int, c_int, c_uint64, c_int, c_int], c_void_p)
         _lib.register("dtm_loader_next", [c_void_p, c_void_p, c_void_p], c_int)
+        _lib.register("dtm_loader_ring_start", [c_void_p, POINTER(c_void_p), c_int, c_uint64], c_int)
+        _lib.register("dtm_loader_ring_acquire", [c_void_p], c_int)
+        _lib.register("dtm_loader_ring_release", [c_void_p, c_int], c_int)
         _lib.register("dtm_loader_records_read", [c_void_p], c_uint64)
         _lib.register("dtm_loader_destroy", [c_void_p], None)
         return _lib.load()
@@ -60,10 +63,19 @@ def _native_loader_lib():
 class NativeRecordBatches:
     """The same stream as :class:`TFRecordBatches`, produced by the C++ pipeline (csrc/io/record_loader.cpp): reader
     threads, CRC checks, Example parsing and the shuffle queue run outside the interpreter, and a batch is written straight
-    into one packed buffer (pixels | padding | labels) that ``NativeEngine.stage_packed`` ships with a single H2D copy."""
+    into one packed buffer (pixels | padding | labels) that ``NativeEngine.stage_packed`` ships with a single H2D copy.
+
+    ``prefetch_batches`` >= 2 (default 4) turns on the loader's batch ring: one more C++ thread assembles whole batches
+    into that many (pinned) buffers ahead of the caller, and ``next_packed`` only swaps buffers - the trainer's thread no
+    longer spends the ~75 us a 512-image dequeue costs.  A returned buffer stays untouched for the next
+    ``prefetch_batches - 2`` calls; a caller that copies it asynchronously calls :meth:`mark_in_flight` with the copy's
+    stream, and the buffer then goes back to the ring as soon as that copy has finished (never before).
+    ``prefetch_batches=0``: every call dequeues into a fresh buffer of its own."""
 
     def __init__(self, lib, filenames: list[str], batch_size: int, image_bytes: int, *, num_threads: int = 2, seed: int = 0,
-                 shuffle: bool = True, min_after_dequeue: int = MIN_AFTER_DEQUEUE, pin: bool = False):
+                 shuffle: bool = True, min_after_dequeue: int = MIN_AFTER_DEQUEUE, pin: bool = False,
+                 prefetch_batches: int = 4):
+        import collections
         import ctypes
 
         self._lib = lib
@@ -79,16 +91,49 @@ class NativeRecordBatches:
                                         min_after_dequeue)
         if not self._h:
             raise ValueError(lib.dtm_last_error().decode())
+        self._ring: list[torch.Tensor] = []
+        self._out = collections.deque()                           # [buffer index, CUDA event or None], oldest first
+        if prefetch_batches >= 2:
+            self._ring = [torch.empty(self.packed_bytes, dtype=torch.uint8, pin_memory=self.pin) for _ in range(prefetch_batches)]
+            ptrs = (ctypes.c_void_p * prefetch_batches)(*[t.data_ptr() for t in self._ring])
+            if lib.dtm_loader_ring_start(self._h, ptrs, prefetch_batches, self.label_offset) != 0:
+                raise ValueError(lib.dtm_last_error().decode())
 
     def next_packed(self) -> torch.Tensor:
-        buf = torch.empty(self.packed_bytes, dtype=torch.uint8, pin_memory=self.pin)
-        base = buf.data_ptr()
-        if self._lib.dtm_loader_next(self._h, base, base + self.label_offset) != 0:
+        if not self._ring:
+            buf = torch.empty(self.packed_bytes, dtype=torch.uint8, pin_memory=self.pin)
+            base = buf.data_ptr()
+            if self._lib.dtm_loader_next(self._h, base, base + self.label_offset) != 0:
+                raise ValueError(self._lib.dtm_last_error().decode())
+            return buf
+        # hand back what the caller is done with: buffers whose marked copy has finished, and - so that the ring's thread
+        # always has a buffer to fill - the oldest ones beyond prefetch_batches - 2 (waiting for their copy if marked)
+        while self._out:
+            idx, ev = self._out[0]
+            done = ev is not None and ev.query()
+            if not done and len(self._out) < len(self._ring) - 1:
+                break
+            if ev is not None and not done:
+                ev.synchronize()
+            self._out.popleft()
+            self._lib.dtm_loader_ring_release(self._h, idx)
+        idx = self._lib.dtm_loader_ring_acquire(self._h)
+        if idx < 0:
             raise ValueError(self._lib.dtm_last_error().decode())
-        return buf
+        self._out.append([idx, None])
+        return self._ring[idx]
+
+    def mark_in_flight(self, stream) -> None:
+        """The buffer returned last is being copied on ``stream``: keep it out of the ring until that copy is done."""
+        if self._ring and self._out and torch.cuda.is_available():
+            ev = torch.cuda.Event()
+            ev.record(stream)
+            self._out[-1][1] = ev
 
     def next(self) -> tuple[torch.Tensor, torch.Tensor]:
         buf = self.next_packed()
+        if self._ring:
+            buf = buf.clone()                     # callers of next() keep their batches; only next_packed() lends ring buffers
         return buf[:self.B * self.image_bytes].view(self.B, self.image_bytes), buf[self.label_offset:].view(torch.int32)
 
     @property

@@ -90,6 +90,8 @@ class DeviceFeeder:
             self.copy_stream.wait_event(self.free[slot])
         if self._packed:
             self.engine.stage_packed(slot, self.source.next_packed(), stream=self.copy_stream)
+            if hasattr(self.source, "mark_in_flight"):           # ring buffers go back to the loader when the copy is done
+                self.source.mark_in_flight(self.copy_stream)
         else:
             images, labels = self.source.next()
             self.engine.stage_batch(slot, images, labels, stream=self.copy_stream)

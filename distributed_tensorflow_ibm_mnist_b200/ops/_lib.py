@@ -10,7 +10,7 @@ import os
 from ctypes import c_char_p, c_float, c_int, c_uint32, c_uint64, c_void_p
 from pathlib import Path
 
-ABI_VERSION = 10
+ABI_VERSION = 11
 _LIB = None
 _LIB_PATH = Path(__file__).resolve().parent.parent / "_native" / "libdtm_b200.so"
 

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define DTM_ABI_VERSION 10
+#define DTM_ABI_VERSION 11
 
 /* GEMM epilogues */
 #define DTM_EPI_STORE_F32 0      /* D(fp32)  = alpha * acc          (split-K: red.add into pre-zeroed D) */
@@ -235,6 +235,14 @@ uint32_t dtm_crc32c(const char* data, size_t n, uint32_t crc);
 void* dtm_loader_create(const char* const* files, int n_files, int batch, int image_bytes, int num_threads, uint64_t seed,
                         int shuffle, int min_after_dequeue);
 int dtm_loader_next(void* loader, uint8_t* pixels_out, int32_t* labels_out);
+/* Batch ring: after dtm_loader_ring_start a thread of the loader fills the caller's n_buffers (>= 2) buffers - each
+ * label_offset + 4*batch bytes, pixels at 0 and int32 labels at label_offset, typically pinned - with whole batches ahead
+ * of the caller.  dtm_loader_ring_acquire blocks for the next filled buffer and returns its index (-1: error, see
+ * dtm_last_error); the buffer belongs to the caller until dtm_loader_ring_release(index) (e.g. once its H2D copy has
+ * finished).  dtm_loader_next is not available while a ring runs. */
+int dtm_loader_ring_start(void* loader, uint8_t* const* buffers, int n_buffers, uint64_t label_offset);
+int dtm_loader_ring_acquire(void* loader);
+int dtm_loader_ring_release(void* loader, int index);
 uint64_t dtm_loader_records_read(void* loader);
 void dtm_loader_destroy(void* loader);
 

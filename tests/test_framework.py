@@ -550,6 +550,51 @@ def test_native_loader_mixed_record_shapes(tmp_path):
     ds.close()
 
 
+def test_native_loader_batch_ring_lends_buffers(tmp_path):
+    """Batch ring of the C++ loader: batches arrive in the same order as from the caller-thread dequeue, a lent buffer is
+    not rewritten during the next prefetch_batches - 2 calls, and the ring and the direct call exclude each other."""
+    from distributed_tensorflow_ibm_mnist_b200.data import readers
+    from distributed_tensorflow_ibm_mnist_b200.formats import tfrecord
+
+    lib = readers._native_loader_lib()
+    if lib is None:
+        pytest.skip("libdtm_b200.so not built")
+    p = str(tmp_path / "d.tfrecord")
+    tfrecord.write_mnist_tfrecord(p, [bytes([i % 256, i // 256]) + bytes(782) for i in range(700)], [i % 10 for i in range(700)])
+
+    def ids(buf, ds):
+        px = buf[:ds.B * 784].view(ds.B, 784)
+        return [int(a) + 256 * int(b) for a, b in zip(px[:, 0], px[:, 1])]
+
+    ring = readers.TFRecordBatches([p], 20, 784, shuffle=False, native=True, prefetch_batches=4)
+    direct = readers.TFRecordBatches([p], 20, 784, shuffle=False, native=True, prefetch_batches=0)
+    held = []
+    for b in range(40):                                  # 800 records: runs into the second epoch
+        buf = ring.next_packed()
+        want = [(b * 20 + j) % 700 for j in range(20)]
+        assert ids(buf, ring) == want == ids(direct.next_packed(), direct)
+        assert [int(v) for v in buf[ring.label_offset:].view(torch.int32)] == [w % 10 for w in want]
+        held.append((buf, want))
+        for old, old_want in held[-3:]:                  # this buffer and the two lent before it are still intact
+            assert ids(old, ring) == old_want
+    assert len({h[0].data_ptr() for h in held}) == 4     # four buffers go round
+    assert lib.dtm_loader_next(ring._h, held[0][0].data_ptr(), held[0][0].data_ptr() + ring.label_offset) != 0
+    assert b"ring" in lib.dtm_last_error()
+    ring.close()
+    direct.close()
+    # shuffled through the ring: pairs stay together, nothing of the first epoch twice (the pipeline looks ahead at most
+    # 2 x 128 chunk records + capacity 88 + ring 48 + batch 16 = 408 records: 240 delivered + 408 < 700)
+    sh = readers.TFRecordBatches([p], 16, 784, seed=9, min_after_dequeue=40, num_threads=2, native=True, prefetch_batches=3)
+    got = []
+    for _ in range(15):
+        buf = sh.next_packed()
+        i = ids(buf, sh)
+        assert [int(v) for v in buf[sh.label_offset:].view(torch.int32)] == [k % 10 for k in i]
+        got += i
+    assert len(set(got)) == len(got) == 240 and got != sorted(got)
+    sh.close()
+
+
 def test_image_preprocessing_helpers():
     from distributed_tensorflow_ibm_mnist_b200.data import readers
 

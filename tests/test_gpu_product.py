@@ -327,3 +327,70 @@ def test_convergence_bf16_engine_tracks_fp32_engine():
     assert np.abs(sn - sr).max() < 0.08 * max(1.0, sr.max()), (np.abs(sn - sr).max(), sn[-1], sr[-1])
     assert sn[-1] < 0.25 * sn[0] and sr[-1] < 0.25 * sr[0]            # both learned
     assert np.mean(an[-20:]) > 0.9 and abs(np.mean(an[-20:]) - np.mean(ar[-20:])) < 0.03
+
+
+def test_tfrecord_training_through_feeder_and_batch_ring(tmp_path):
+    """Real-data input on the GPU: TFRecords -> C++ loader (batch ring of pinned buffers) -> DeviceFeeder's copy stream ->
+    device slots.  (a) With a slow consumer and the smallest ring every lent buffer is recycled while copies are still
+    queued: each step must still see exactly its batch.  (b) The native engine trains from the same files."""
+    from distributed_tensorflow_ibm_mnist_b200.data import readers
+    from distributed_tensorflow_ibm_mnist_b200.data.synthetic import DeviceFeeder, SyntheticMnist
+    from distributed_tensorflow_ibm_mnist_b200.formats import tfrecord
+    from distributed_tensorflow_ibm_mnist_b200.models import presets
+    from distributed_tensorflow_ibm_mnist_b200.train.native_engine import NativeEngine
+
+    B, n = 64, 64 * 24
+    src = SyntheticMnist(B, 784, pool_batches=24, seed=2, separable=True, pin=False)
+    imgs, labels = [], []
+    for _ in range(24):
+        x, y = src.next()
+        imgs += [bytes(r.numpy().tobytes()) for r in x.view(B, 784)]
+        labels += [int(v) for v in y]
+    path = str(tmp_path / "train.tfrecord")
+    assert tfrecord.write_mnist_tfrecord(path, imgs, labels) == n
+
+    class Probe:                                  # an engine that only records what each step was given
+        def __init__(self):
+            self.B, self.device = B, torch.device("cuda", 0)
+            self.spec = presets.make_spec("baseline")
+            self.packed_label_offset = B * 784
+            self.xy = [torch.zeros(B * 784 + 4 * B, dtype=torch.uint8, device="cuda") for _ in range(2)]
+            self.seen = []
+
+        def stage_packed(self, slot, packed, stream=None):
+            with torch.cuda.stream(stream):
+                self.xy[slot].copy_(packed, non_blocking=True)
+
+        def train_step(self, slot):
+            torch.cuda._sleep(400_000)           # ~0.2 ms: the host runs far ahead of the GPU
+            self.seen.append(self.xy[slot].clone())
+
+    probe = Probe()
+    ds = readers.TFRecordBatches([path], B, 784, shuffle=False, native=True, pin=True, prefetch_batches=2)
+    assert isinstance(ds, readers.NativeRecordBatches) and ds.label_offset == probe.packed_label_offset
+    feeder = DeviceFeeder(probe, ds)
+    assert feeder._packed
+    for _ in range(60):
+        feeder.step()
+    torch.cuda.synchronize()
+    for k, got in enumerate(probe.seen):
+        lo = (k * B) % n
+        want = b"".join(imgs[lo:lo + B])
+        assert bytes(got[:B * 784].cpu().numpy().tobytes()) == want, k
+        assert [int(v) for v in got[B * 784:].view(torch.int32).cpu()] == labels[lo:lo + B], k
+    ds.close()
+
+    from distributed_tensorflow_ibm_mnist_b200.models import oracle
+
+    eng = NativeEngine(presets.make_spec("baseline"), B, optimizer="adam", base_lr=1e-3, seed=3, use_graph=True)
+    eng.load_params(oracle.init_params(eng.spec, seed=4))
+    ds = readers.TFRecordBatches([path], B, 784, seed=4, min_after_dequeue=256, native=True, pin=True)
+    feeder = DeviceFeeder(eng, ds)
+    first = None
+    for i in range(150):
+        feeder.step()
+        if i == 4:
+            first = eng.metrics()["cross_entropy"]
+    last = eng.metrics()["cross_entropy"]
+    ds.close()
+    assert np.isfinite(first) and last < 0.7 * first, (first, last)

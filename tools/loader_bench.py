@@ -4,8 +4,8 @@
     python tools/loader_bench.py [--threads 1 2 4] [--records 60000] [--batch 512] [--seconds 2.0]
 
 Writes one MNIST-shaped TFRecord file (28 x 28 x 1 uint8 `image_raw` + int64 `label`, the layout convert_mnist.py
-produces) into a temporary directory, then times `next_packed()` - the call main.py's input thread makes - after the
-shuffle queue has filled.  Host-only: no GPU needed.
+produces) into a temporary directory, then times `next_packed()` - the call the trainer's feeder makes - after the shuffle
+queue has filled, with the loader's batch ring (a C++ thread assembles batches ahead) and without it.  Host-only: no GPU needed.
 """
 import argparse
 import json
@@ -38,6 +38,8 @@ def main():
     ap.add_argument("--batch", type=int, default=512)
     ap.add_argument("--seconds", type=float, default=3.0)
     ap.add_argument("--channels", type=int, default=1)
+    ap.add_argument("--prefetch", type=int, nargs="+", default=[4, 0],
+                    help="batch-ring sizes to measure (0 = the caller's thread dequeues)")
     args = ap.parse_args()
     image_bytes = 28 * 28 * args.channels
     rng = np.random.default_rng(0)
@@ -51,8 +53,8 @@ def main():
                     w.write(encode_example({"image_raw": rng.integers(0, 256, image_bytes, dtype=np.uint8).tobytes(),
                                             "label": int(i % 10), "height": 28, "width": 28, "depth": args.channels}))
         rows = []
-        for t in args.threads:
-            it = TFRecordBatches(names, args.batch, image_bytes, num_threads=t, seed=1)
+        for t, ring in [(t, r) for r in args.prefetch for t in args.threads]:
+            it = TFRecordBatches(names, args.batch, image_bytes, num_threads=t, seed=1, prefetch_batches=ring)
             for _ in range(8):
                 it.next_packed()
             rates = []                                   # the host is shared: report the median and the best of five windows
@@ -68,8 +70,8 @@ def main():
             steal = (_steal_jiffies() - steal0) / 100.0 / args.seconds
             it.close()
             rates.sort()
-            rows.append({"threads": t, "images_per_s": round(rates[2]), "best_window": round(rates[-1]), "worst_window": round(rates[0]),
-                         "consumer_cpu_ns_per_image": round(cpu_ns), "stolen_cpu_seconds_per_second": round(steal, 2),
+            rows.append({"threads": t, "prefetch_batches": ring, "images_per_s": round(rates[2]), "best_window": round(rates[-1]), "worst_window": round(rates[0]),
+                         "caller_cpu_ns_per_image": round(cpu_ns), "stolen_cpu_seconds_per_second": round(steal, 2),
                          "native": type(it).__name__ == "NativeRecordBatches"})
             print(json.dumps(rows[-1]), flush=True)
     return rows
