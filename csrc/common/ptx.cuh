@@ -313,6 +313,17 @@ DTM_DEVICE float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); 
 // (profiles/stall_report_r1.md: 10-22 % of the GEMM / dgrad stall samples sat on exactly those loads).
 DTM_DEVICE void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
+// LRN's s^(-3/4) for s >= 1 (tf.nn.lrn with beta = 0.75, bias 1): r = s^(-1/2) from MUFU.RSQ, then r * sqrt(r) with
+// MUFU.SQRT - two special-function instructions and one multiply where __powf costs lg2 + mul + ex2 and range fix-ups;
+// r * r is 1 / s for the backward pass, which would otherwise divide.
+DTM_DEVICE float lrn_pow_m075(float s, float* inv_s = nullptr) {
+  float r, q;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(s));
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(q) : "f"(r));
+  if (inv_s) *inv_s = r * r;
+  return r * q;
+}
+
 DTM_DEVICE float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -37,6 +37,7 @@ constexpr int S1_F_BYTES = S1_F_ROWS * S1_F_ROW_BYTES;          // one (channel,
 constexpr int S1_ACC = 2;                       // TMEM accumulator ring: 2 groups x (4 positions x 32 columns)
 constexpr int S1_KCH = 6;                       // K chunks per channel (kh 0..4 + one zero chunk) -> 3 MMAs of K = 16
 constexpr float S1_LRN_BIAS = 1.0f, S1_LRN_ALPHA = 0.001f / 9.0f, S1_LRN_BETA = 0.75f;
+static_assert(S1_LRN_BETA == 0.75f, "the LRN epilogue computes s^-0.75 with lrn_pow_m075");
 
 template <int CIN> struct S1Geom {
   static constexpr int F_SET = 2 * CIN * S1_F_BYTES;                       // both parities, every channel: one image
@@ -242,7 +243,7 @@ conv1_sw_kernel(const void* __restrict__ x, int in_is_float, const float* __rest
 #pragma unroll
             for (int dd = -4; dd <= 4; ++dd)
               if (c + dd >= 0 && c + dd < S1_OUT) s += act[c + dd] * act[c + dd];
-            yv[c] = act[c] * __powf(S1_LRN_BIAS + S1_LRN_ALPHA * s, -S1_LRN_BETA);
+            yv[c] = act[c] * lrn_pow_m075(S1_LRN_BIAS + S1_LRN_ALPHA * s);
           }
 #pragma unroll
           for (int c = 0; c < S1_OUT; ++c) best[c] = yv[c];

@@ -35,6 +35,7 @@ constexpr int T1_SLOTS = 4;             // A-tile ring
 constexpr int T1_ACC = 2;               // TMEM accumulator ring: 2 groups x (4 positions x 32 columns)
 
 constexpr float T1_LRN_BIAS = 1.0f, T1_LRN_ALPHA = 0.001f / 9.0f, T1_LRN_BETA = 0.75f;
+static_assert(T1_LRN_BETA == 0.75f, "the LRN epilogue computes s^-0.75 with lrn_pow_m075");
 
 template <int CIN> struct T1Geom {
   static constexpr int K = 25 * CIN;
@@ -235,7 +236,7 @@ conv1_tc_kernel(const void* __restrict__ x, int in_is_float, const float* __rest
 #pragma unroll
             for (int dd = -4; dd <= 4; ++dd)
               if (c + dd >= 0 && c + dd < T1_OUT) s += act[c + dd] * act[c + dd];
-            y[c] = act[c] * __powf(T1_LRN_BIAS + T1_LRN_ALPHA * s, -T1_LRN_BETA);
+            y[c] = act[c] * lrn_pow_m075(T1_LRN_BIAS + T1_LRN_ALPHA * s);
           }
 #pragma unroll
           for (int c = 0; c < T1_OUT; ++c) best[c] = y[c];

@@ -46,9 +46,10 @@ DTM_DEVICE void dg_lrn_backward_half(const float (&dy)[32], const float (&a)[32]
     for (int d = -4; d <= 4; ++d)
       if (c + d >= 0 && c + d < 32) ss += a[c + d] * a[c + d];
     ss = 1.0f + alpha * ss;
-    const float pw = __powf(ss, -beta);
+    float inv_ss;
+    const float pw = lrn_pow_m075(ss, &inv_ss);
     sp[c] = pw;
-    t1[c] = dy[c] * a[c] * pw / ss;
+    t1[c] = dy[c] * a[c] * pw * inv_ss;
   }
 #pragma unroll
   for (int j = 0; j < 16; ++j) {

@@ -30,6 +30,7 @@ constexpr int C2_SMEM = C2_W_BYTES + PL_GUARD_BYTES + C2_BUFS * C2_IMG_BYTES + P
 constexpr float LRN2_BIAS = 1.0f;
 constexpr float LRN2_ALPHA = 0.001f / 9.0f;
 constexpr float LRN2_BETA = 0.75f;
+static_assert(LRN2_BETA == 0.75f, "the LRN epilogue computes s^-0.75 with lrn_pow_m075");
 
 // Epilogue width: the pooling/arg-max code is a long dependent chain (3 shuffles + compares per channel), and with one
 // epilogue warp per scheduler it, not the tensor core, set the kernel time (ncu: tensor pipe 24 % active).  Without
@@ -212,7 +213,7 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
             float sum = 0.0f;
 #pragma unroll
             for (int d = 0; d < 9; ++d) sum += ext[j + d];
-            v[j] *= __powf(LRN2_BIAS + LRN2_ALPHA * sum, -LRN2_BETA);
+            v[j] *= lrn_pow_m075(LRN2_BIAS + LRN2_ALPHA * sum);
           }
         }
         // 2x2 max-pool across lanes l, l^1 (w+1), l^16 (h+1), l^17

@@ -131,9 +131,10 @@ unpool2_lrn_kernel(const __nv_bfloat16* __restrict__ dp2, const uint8_t* __restr
 #pragma unroll
       for (int d = 0; d < 9; ++d) s += ext[i + d];
       s = 1.0f + alpha * s;
-      const float pw = __powf(s, -beta);
+      float inv_s;
+      const float pw = lrn_pow_m075(s, &inv_s);
       sp[i] = pw;
-      t1[i] = g[i] * a[i] * pw / s;
+      t1[i] = g[i] * a[i] * pw * inv_s;
     }
     widen(t1, ext);
     float o[8];
