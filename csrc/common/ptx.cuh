@@ -324,6 +324,20 @@ DTM_DEVICE float lrn_pow_m075(float s, float* inv_s = nullptr) {
   return r * q;
 }
 
+// LRN's channel window: out[j] = ext[j] + ... + ext[j + 8] for N consecutive channels whose values (squares, or the
+// backward pass's t terms) sit in ext[4 + j] with four neighbours (zero outside the tensor) on either side.  Running prefix
+// sums make that one addition and one subtraction per channel instead of eight additions; the prefix holds at most N + 8
+// terms of one sign class of magnitude, so the difference is exact to a few ulp of the largest prefix.
+template <int N>
+DTM_DEVICE void window9_sums(const float (&ext)[N + 8], float (&out)[N]) {
+  float p[N + 9];
+  p[0] = 0.0f;
+#pragma unroll
+  for (int k = 0; k < N + 8; ++k) p[k + 1] = p[k] + ext[k];
+#pragma unroll
+  for (int j = 0; j < N; ++j) out[j] = p[j + 9] - p[j];
+}
+
 DTM_DEVICE float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

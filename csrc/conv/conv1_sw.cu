@@ -237,14 +237,14 @@ conv1_sw_kernel(const void* __restrict__ x, int in_is_float, const float* __rest
           float act[S1_OUT], yv[S1_OUT];
 #pragma unroll
           for (int c = 0; c < S1_OUT; ++c) act[c] = __bfloat162float(__float2bfloat16(best[c]));   // what the backward pass sees
+          float ext[S1_OUT + 8], win[S1_OUT];
 #pragma unroll
-          for (int c = 0; c < S1_OUT; ++c) {
-            float s = 0.0f;
+          for (int k = 0; k < 4; ++k) ext[k] = ext[S1_OUT + 4 + k] = 0.0f;
 #pragma unroll
-            for (int dd = -4; dd <= 4; ++dd)
-              if (c + dd >= 0 && c + dd < S1_OUT) s += act[c + dd] * act[c + dd];
-            yv[c] = act[c] * lrn_pow_m075(S1_LRN_BIAS + S1_LRN_ALPHA * s);
-          }
+          for (int c = 0; c < S1_OUT; ++c) ext[4 + c] = act[c] * act[c];
+          window9_sums<S1_OUT>(ext, win);
+#pragma unroll
+          for (int c = 0; c < S1_OUT; ++c) yv[c] = act[c] * lrn_pow_m075(S1_LRN_BIAS + S1_LRN_ALPHA * win[c]);
 #pragma unroll
           for (int c = 0; c < S1_OUT; ++c) best[c] = yv[c];
         }

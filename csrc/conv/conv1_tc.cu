@@ -230,14 +230,14 @@ conv1_tc_kernel(const void* __restrict__ x, int in_is_float, const float* __rest
           float act[T1_OUT], y[T1_OUT];
 #pragma unroll
           for (int c = 0; c < T1_OUT; ++c) act[c] = __bfloat162float(__float2bfloat16(best[c]));   // what the backward pass sees
+          float ext[T1_OUT + 8], win[T1_OUT];
 #pragma unroll
-          for (int c = 0; c < T1_OUT; ++c) {
-            float s = 0.0f;
+          for (int k = 0; k < 4; ++k) ext[k] = ext[T1_OUT + 4 + k] = 0.0f;
 #pragma unroll
-            for (int dd = -4; dd <= 4; ++dd)
-              if (c + dd >= 0 && c + dd < T1_OUT) s += act[c + dd] * act[c + dd];
-            y[c] = act[c] * lrn_pow_m075(T1_LRN_BIAS + T1_LRN_ALPHA * s);
-          }
+          for (int c = 0; c < T1_OUT; ++c) ext[4 + c] = act[c] * act[c];
+          window9_sums<T1_OUT>(ext, win);
+#pragma unroll
+          for (int c = 0; c < T1_OUT; ++c) y[c] = act[c] * lrn_pow_m075(T1_LRN_BIAS + T1_LRN_ALPHA * win[c]);
 #pragma unroll
           for (int c = 0; c < T1_OUT; ++c) best[c] = y[c];
         }

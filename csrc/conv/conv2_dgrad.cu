@@ -36,29 +36,31 @@ template <int HALF>
 DTM_DEVICE void dg_lrn_backward_half(const float (&dy)[32], const float (&a)[32], float (&out)[16]) {
   constexpr int J0 = HALF * 16;
   constexpr int T0 = J0 - 4 < 0 ? 0 : J0 - 4, T1 = J0 + 20 > 32 ? 32 : J0 + 20;    // channels whose t_c is needed
+  constexpr int NT = T1 - T0;                                                      // 20
   const float alpha = 0.001f / 9.0f, beta = 0.75f;
-  float t1[32], sp[32];
+  float ext[NT + 8], ss[NT], sp[NT];
 #pragma unroll
-  for (int c = 0; c < 32; ++c) {
-    if (c < T0 || c >= T1) { t1[c] = 0.0f; sp[c] = 0.0f; continue; }
-    float ss = 0.0f;
-#pragma unroll
-    for (int d = -4; d <= 4; ++d)
-      if (c + d >= 0 && c + d < 32) ss += a[c + d] * a[c + d];
-    ss = 1.0f + alpha * ss;
-    float inv_ss;
-    const float pw = lrn_pow_m075(ss, &inv_ss);
-    sp[c] = pw;
-    t1[c] = dy[c] * a[c] * pw * inv_ss;
+  for (int k = 0; k < NT + 8; ++k) {                       // squares of channels T0 - 4 .. T1 + 3, zero outside 0..31
+    const int c = T0 - 4 + k;
+    ext[k] = (c >= 0 && c < 32) ? a[c < 0 ? 0 : (c > 31 ? 31 : c)] * a[c < 0 ? 0 : (c > 31 ? 31 : c)] : 0.0f;
   }
+  window9_sums<NT>(ext, ss);
+  float text[16 + 8];                                      // t of channels J0 - 4 .. J0 + 19, zero outside T0..T1-1
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    float acc = 0.0f;
+  for (int m = 0; m < 24; ++m) text[m] = 0.0f;
 #pragma unroll
-    for (int d = -4; d <= 4; ++d)
-      if (J0 + j + d >= 0 && J0 + j + d < 32) acc += t1[J0 + j + d];
-    out[j] = dy[J0 + j] * sp[J0 + j] - 2.0f * alpha * beta * a[J0 + j] * acc;
+  for (int i = 0; i < NT; ++i) {
+    const int c = T0 + i;
+    float inv_s;
+    const float s = 1.0f + alpha * ss[i];
+    const float pw = lrn_pow_m075(s, &inv_s);
+    sp[i] = pw;
+    text[c - (J0 - 4)] = dy[c] * a[c] * pw * inv_s;
   }
+  float acc[16];
+  window9_sums<16>(text, acc);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) out[j] = dy[J0 + j] * sp[J0 + j - T0] - 2.0f * alpha * beta * a[J0 + j] * acc[j];
 }
 
 // The non-LRN kernel declares 512 threads (it is launched with 384) to cap itself at 128 registers per thread: 384 x 128 =

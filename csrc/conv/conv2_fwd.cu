@@ -208,13 +208,10 @@ conv2_fwd_kernel(const uint8_t* __restrict__ p1_planes, const __nv_bfloat16* __r
           }
 #pragma unroll
           for (int j = 0; j < CH; ++j) ext[4 + j] = v[j] * v[j];
+          float win[CH];
+          window9_sums<CH>(ext, win);
 #pragma unroll
-          for (int j = 0; j < CH; ++j) {
-            float sum = 0.0f;
-#pragma unroll
-            for (int d = 0; d < 9; ++d) sum += ext[j + d];
-            v[j] *= lrn_pow_m075(LRN2_BIAS + LRN2_ALPHA * sum);
-          }
+          for (int j = 0; j < CH; ++j) v[j] *= lrn_pow_m075(LRN2_BIAS + LRN2_ALPHA * win[j]);
         }
         // 2x2 max-pool across lanes l, l^1 (w+1), l^16 (h+1), l^17
         __nv_bfloat16* p2_dst = p2 + (static_cast<size_t>(img) * 49 + ph * 7 + pw) * C2_OUT + c0;

@@ -125,25 +125,22 @@ unpool2_lrn_kernel(const __nv_bfloat16* __restrict__ dp2, const uint8_t* __restr
 #pragma unroll
     for (int i = 0; i < 8; ++i) sq[i] = a[i] * a[i];
     widen(sq, ext);
+    float win[8];
+    window9_sums<8>(ext, win);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      float s = 0.0f;
-#pragma unroll
-      for (int d = 0; d < 9; ++d) s += ext[i + d];
-      s = 1.0f + alpha * s;
+      const float s = 1.0f + alpha * win[i];
       float inv_s;
       const float pw = lrn_pow_m075(s, &inv_s);
       sp[i] = pw;
       t1[i] = g[i] * a[i] * pw * inv_s;
     }
     widen(t1, ext);
+    window9_sums<8>(ext, win);
     float o[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      float acc = 0.0f;
-#pragma unroll
-      for (int d = 0; d < 9; ++d) acc += ext[i + d];
-      const float da = g[i] * sp[i] - 2.0f * alpha * beta * a[i] * acc;
+      const float da = g[i] * sp[i] - 2.0f * alpha * beta * a[i] * win[i];
       o[i] = a[i] > 0.0f ? da : 0.0f;
     }
     if (active) {

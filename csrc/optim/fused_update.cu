@@ -48,7 +48,11 @@ fused_update_stride_kernel(const dtm_update_config cfg, dtm_train_state* __restr
   if (cur_seg >= 0) atomicAdd(&s_wl[cur_seg], cur_sq);
   __syncthreads();
   if (threadIdx.x < cfg.n_segments && s_wl[threadIdx.x] != 0.0f) atomicAdd(&st->wl_sum[threadIdx.x], s_wl[threadIdx.x]);
-  // last block to finish closes the step
+  // last block to finish closes the step.  A launch that does not close it (the early update of the fc bucket) takes no
+  // ticket: with the full grid that was 1184 returning atomics on one address, ~14 ns apiece in the L2, during which the
+  // finished CTAs kept their SM slots and the conv backward kernel queued behind them could not start (reference preset:
+  // the update spanned 48 us on the timeline for 6 us of memory traffic).
+  if (!do_finish) return;
   __threadfence();
   __syncthreads();
   __shared__ unsigned int s_last;
@@ -57,7 +61,7 @@ fused_update_stride_kernel(const dtm_update_config cfg, dtm_train_state* __restr
   if (s_last) {   // the whole CTA: finish_step spreads the bookkeeping over its threads
     __threadfence();
     if (threadIdx.x == 0) st->ticket = 0;
-    if (do_finish) finish_step(cfg, st, u.lr_plain);
+    finish_step(cfg, st, u.lr_plain);
   }
 }
 

@@ -108,9 +108,12 @@ class NativeEngine:
         self._pdl = 2 if small else 0
         # grid cap of the early optimizer update: one CTA per SM.  conv2_dgrad is held to 128 registers so that exactly one
         # update CTA fits beside it on every SM - the two kernels run side by side instead of taking turns (179.6 -> 169.6
-        # us).  No cap for wide (the update is the long pole) nor for the LRN preset (measured slower: 406 -> 429 us).
+        # us).  The LRN preset's backward kernels carry heavier epilogues and its fc bucket is small: two update CTAs per SM
+        # finish before conv2_dgrad needs the SMs (same box, us per step: uncapped 230.5, 148 CTAs 231, 222: 217.2,
+        # 296: 217.0, 444: 227.5, 592: 225.5).  No cap for wide (the update is the long pole).
         sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
-        self._early_update_ctas = int(env.get("DTM_EARLY_UPDATE_CTAS", str(sm_count if (small and not spec.lrn) else 0)))
+        default_cap = (2 * sm_count if spec.lrn else sm_count) if small else 0
+        self._early_update_ctas = int(env.get("DTM_EARLY_UPDATE_CTAS", str(default_cap)))
         if comm is not None and "DTM_OVERLAP_CTAS" not in env:
             if not small:
                 # wide: the fc bucket's exchange runs ~200 us and is bound by the NVSwitch, not by the CTA count (8-GPU
