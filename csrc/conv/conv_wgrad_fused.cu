@@ -95,7 +95,7 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
   const int first = blockIdx.x, stride = gridDim.x;
   const int n_it = (batch - first + stride - 1) / stride;
   // conv1 images of this CTA: iterations with (it & 1) != y  (y = 1, the 12-tap group, takes the even ones)
-  const int n_c1 = !conv1_on ? 0 : (y == 1 ? (n_it + 1) / 2 : n_it / 2);
+  const int n_c1 = !(conv1_on & 1) ? 0 : (y == 1 ? (n_it + 1) / 2 : n_it / 2);
 
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < FW_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
@@ -166,7 +166,7 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
         if (it == 0) fw_issue_conv2<true>(tmem_base, dz_base, p1_base, tap0, ntaps, idesc);
         else         fw_issue_conv2<false>(tmem_base, dz_base, p1_base, tap0, ntaps, idesc);
         umma_commit(&empty_bar[s]);
-        if (conv1_on && (it & 1) != y) {
+        if ((conv1_on & 1) && (it & 1) != y) {
           mbar_wait(&c1_full, j & 1, 33);
           tc_fence_after();
           if (!(conv1_on & 2)) {
@@ -191,7 +191,7 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
     const int bt = threadIdx.x - 64;        // 0..191
     int it = 0, j = 0;
     for (int img = first; img < batch; img += stride, ++it) {
-      if (!conv1_on || (it & 1) == y) continue;
+      if (!(conv1_on & 1) || (it & 1) == y) continue;
       // global loads of this image first: they are in flight while the previous conv1 image's MMAs are awaited
       constexpr int XWORDS = CIN * 196;                            // 784 * C_in bytes, pixels interleaved (HWC)
       constexpr int NXW = (XWORDS + FW_BUILDERS - 1) / FW_BUILDERS;
@@ -279,8 +279,13 @@ conv_wgrad_fused_kernel(const uint8_t* __restrict__ p1_planes, const uint8_t* __
       mbar_wait_warp(&done_bar, 0, 32);
       tc_fence_after();
       const int row = q * 16 + lane;  // accumulator row (M = 64: lanes 0-15 of each quadrant), valid for lane < 16
+      // All CTAs of a tap group finish their MMAs together and add into the same 26 K floats: each starts at another tap,
+      // so that at any moment the grid's red.add traffic is spread over 13 x 32 cache lines instead of 32 (same-box A/B with
+      // DTM_FW_NO_STAGGER=1: 142.46 against 142.60 us per step - the L2 was not the limit here; kept, it costs nothing)
+      const int rot = (conv1_on & 8) ? 0 : static_cast<int>(blockIdx.x) % ntaps;
 #pragma unroll 1
-      for (int tl = 0; tl < ntaps; ++tl) {
+      for (int t = 0; t < ntaps; ++t) {
+        const int tl = t + rot < ntaps ? t + rot : t + rot - ntaps;
         uint32_t r[32];
         tmem_ld_x32(tmem_base + ((q * 32u) << 16) + tl * FW_CI, r);
         tmem_ld_wait();
@@ -339,7 +344,9 @@ extern "C" int dtm_conv_wgrad_fused(const void* p1_planes, const void* dz2_plane
   // experiment switch (tools/kernel_bench.py): DTM_FW_NO_CONV1=1 leaves the conv1 part out (dw1 / db1 stay untouched)
   // (values 3 / 5 / 7: conv1 pipeline without its MMAs / without the operand building / without both - timing only)
   const char* e = getenv("DTM_FW_NO_CONV1");
-  const int conv1_on = e ? ((e[0] == '1') ? 0 : atoi(e)) : 1;
+  int conv1_on = e ? ((e[0] == '1' && e[1] == 0) ? 0 : atoi(e)) : 1;
+  const char* ns = getenv("DTM_FW_NO_STAGGER");                 // A/B switch: every CTA adds its taps in the same order
+  if (ns && ns[0] == '1') conv1_on |= 8;
   static bool configured[64] = {};     // per device: function attributes belong to a device's context
   const int dev_slot = device_slot();
   if (!configured[dev_slot]) {
