@@ -54,7 +54,12 @@ class StopAtStepHook(Hook):
 
 
 class NanLossHook(Hook):
-    def __init__(self, check_every: int = 10, fail_on_nan_loss: bool = True):
+    """``check_every``: steps between polls.  Both engines keep a STICKY NaN flag (the native one on the device, set by the
+    loss kernel of every step), so a sparse poll only delays the stop, it cannot miss the event.  Every poll of the native
+    engine is a device->host read that drains the queue of launched steps, and with several ranks also a collective of
+    the control plane: every 100 steps (15 ms) that costs well under 1 %; every 10 steps it was 5-10 % of a 150 us step."""
+
+    def __init__(self, check_every: int = 100, fail_on_nan_loss: bool = True):
         self.check_every, self.fail = max(1, check_every), fail_on_nan_loss
 
     def _check(self, loop) -> None:
@@ -170,7 +175,7 @@ class MonitoredTrainingLoop:
     """``with MonitoredTrainingLoop(...) as sess: while not sess.should_stop(): sess.run_step()``."""
 
     def __init__(self, engine, source, *, hooks=(), is_chief=True, saver=None, task_id=0, feeder=None, log_every=100,
-                 verbose_steps=False, out=print, group=None, save_poll_every=50):
+                 verbose_steps=False, out=print, group=None, save_poll_every=100):
         self.engine, self.source = engine, source
         self.hooks = list(hooks)
         self.is_chief, self.saver, self.task_id = is_chief, saver, task_id
@@ -239,8 +244,9 @@ class MonitoredTrainingLoop:
         return cp.any_true(flag)
 
     def _agree(self, flag: bool) -> bool:
-        """The chief's decision, known to every rank."""
-        return bool(self._plane().broadcast_object(bool(flag), 0))
+        """The chief's decision, known to every rank (callers pass False on every other rank: one cheap flag reduction
+        instead of a pickled broadcast)."""
+        return self._plane().any_true(bool(flag))
 
     def summary_tensors(self) -> dict:
         eng = self.engine

@@ -29,7 +29,7 @@ def main() -> int:
     got = plane.exchange_fds([os.open(path, os.O_RDONLY)] if rank == 0 else [])
     assert [len(g) for g in got] == [1] + [0] * (world - 1)
     assert os.pread(got[0][0], 64, 0).decode() == "hello from rank 0"
-    assert plane.all_true(True) and not plane.all_true(rank == 0) and plane.any_true(rank == 1)
+    assert plane.all_true(True) and not plane.all_true(rank == 0) and plane.any_true(rank == 1) and not plane.any_true(False)
     assert plane.broadcast_object({"k": rank}, 1) == {"k": 1}
     dist.destroy_process_group()
     print("FD_EXCHANGE_OK", rank)

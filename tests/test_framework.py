@@ -678,6 +678,71 @@ def test_thread_plane_collectives():
         assert all1 and not all2 and any1 and not any2
 
 
+def test_nan_hook_polls_sparsely_and_stops_all_ranks_together():
+    """NanLossHook (the reference's NanTensorHook(loss), main.py:138): the engines keep a sticky NaN flag, the hook polls it
+    every ``check_every`` steps and at the end; with several ranks the decision is collective - a rank whose own loss is
+    still finite stops on the same step as the rank that saw the NaN, instead of waiting for it in the next exchange."""
+    import threading
+
+    from distributed_tensorflow_ibm_mnist_b200.parallel.control_plane import ThreadPlane
+    from distributed_tensorflow_ibm_mnist_b200.train import trainer
+
+    class Engine:                                   # NaN appears at local step `bad_at` and sticks
+        def __init__(self, bad_at):
+            self.bad_at, self.steps, self.polls = bad_at, 0, 0
+
+        def stage_batch(self, slot, x, y):
+            pass
+
+        def train_step(self, slot):
+            self.steps += 1
+
+        def metrics(self):
+            self.polls += 1
+            bad = self.bad_at is not None and self.steps >= self.bad_at
+            return {"global_step": self.steps, "total_loss": float("nan") if bad else 1.0, "nan": bad}
+
+    class Source:
+        def next(self):
+            return None, None
+
+    def run(engine, hook, plane=None, steps=1000):
+        with trainer.MonitoredTrainingLoop(engine, Source(), hooks=[trainer.StopAtStepHook(steps), hook], group=plane,
+                                           log_every=0, out=lambda *a: None) as sess:
+            while not sess.should_stop():
+                sess.run_step()
+
+    assert trainer.NanLossHook().check_every == 100
+    eng = Engine(bad_at=130)
+    with pytest.raises(trainer.NanLossError, match="NaN loss"):
+        run(eng, trainer.NanLossHook())
+    assert eng.steps == 200 and eng.polls == 1 + 2           # start-step read, polls at 100 and 200; stops at the second
+    eng = Engine(bad_at=7)
+    run(eng, trainer.NanLossHook(check_every=5, fail_on_nan_loss=False))
+    assert eng.steps == 10                                    # request_stop instead of raising
+    eng = Engine(bad_at=None)
+    run(eng, trainer.NanLossHook(), steps=250)
+    assert eng.steps == 250 and eng.polls == 1 + 2 + 1        # ... and the final check in end()
+
+    planes = ThreadPlane.make(2)
+    engines = [Engine(bad_at=None), Engine(bad_at=30)]
+    errors = [None, None]
+
+    def worker(r):
+        try:
+            run(engines[r], trainer.NanLossHook(check_every=20), plane=planes[r], steps=500)
+        except trainer.NanLossError as e:
+            errors[r] = e
+
+    ths = [threading.Thread(target=worker, args=(r,)) for r in range(2)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join(timeout=60)
+    assert all(isinstance(e, trainer.NanLossError) for e in errors)
+    assert engines[0].steps == engines[1].steps == 40         # both at the first poll after the event
+
+
 def test_dist_plane_passes_file_descriptors(tmp_path):
     """How GPU allocation handles travel between worker processes: SCM_RIGHTS over abstract unix sockets, rendezvous over the
     process group (gloo here)."""
