@@ -202,3 +202,37 @@ def test_supervisor_restarts_failed_worker_set_from_checkpoint(tmp_path):
                         "--batch_size=8", "--max_steps=9", "--engine=torch", "--save_checkpoint_secs=-1"], cwd=ROOT,
                        env=dict(ENV, DTM_FAULT_INJECT="0:2"), capture_output=True, text=True, timeout=400)
     assert r.returncode == 43 and "no restarts left" in r.stdout
+
+
+def test_training_from_tfrecord_files_and_loader_bench(tmp_path):
+    """Real-data route of main.py (mnist_input.inputs): --train_data TFRecords -> C++ loader (reader threads, shuffle queue,
+    batch ring) -> engine; and the loader benchmark tool runs on a GPU-less host."""
+    from distributed_tensorflow_ibm_mnist_b200.data.synthetic import SyntheticMnist
+    from distributed_tensorflow_ibm_mnist_b200.formats import tfrecord
+
+    src = SyntheticMnist(32, 784, pool_batches=20, seed=1, separable=True, pin=False)
+    imgs, labels = [], []
+    for _ in range(20):
+        x, y = src.next()
+        imgs += [bytes(r.numpy().tobytes()) for r in x.view(32, 784)]
+        labels += [int(v) for v in y]
+    files = [str(tmp_path / "a.tfrecords"), str(tmp_path / "b.tfrecords")]
+    tfrecord.write_mnist_tfrecord(files[0], imgs[:320], labels[:320])
+    tfrecord.write_mnist_tfrecord(files[1], imgs[320:], labels[320:])
+    train_dir = str(tmp_path / "train")
+    r = _run(["main.py", f"--train_dir={train_dir}", "--model=baseline", "--batch_size=32", "--test_interval=10", "--optimizer=adam",
+              "--base_lr=0.001", "--engine=torch", "--save_checkpoint_secs=0", "--max_steps=45", "--input_threads=3",
+              "--train_data=" + ",".join(files)])
+    assert r.returncode == 0, r.stderr[-2500:]
+    assert "45 steps executed on worker 0." in r.stdout and "image Shape" in r.stdout
+    from distributed_tensorflow_ibm_mnist_b200.formats import events
+
+    evs = events.read_events(glob.glob(os.path.join(train_dir, "log", "events.out.tfevents.*"))[0])
+    losses = [e["scalars"]["train loss"] for e in evs if "train loss" in e["scalars"]]
+    assert len(losses) == 4 and losses[-1] < losses[0]                 # separable classes: the loss falls within 40 steps
+    r = _run(["main.py", f"--train_dir={train_dir}2", "--engine=torch", "--max_steps=2", "--train_data=" + str(tmp_path / "nope.tfrecords")])
+    assert r.returncode != 0 and "Failed to find file" in (r.stderr + r.stdout)     # mnist_input.py:55
+    r = _run(["tools/loader_bench.py", "--records", "3000", "--seconds", "0.5", "--threads", "2", "--prefetch", "3", "0"])
+    assert r.returncode == 0, r.stderr[-1500:]
+    rows = [json.loads(line) for line in r.stdout.strip().splitlines()]
+    assert [row["prefetch_batches"] for row in rows] == [3, 0] and all(row["native"] and row["images_per_s"] > 0 for row in rows)
