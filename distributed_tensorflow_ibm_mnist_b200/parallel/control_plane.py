@@ -45,19 +45,22 @@ class DistPlane:
         self.dist.broadcast_object_list(box, src=self.dist.get_global_rank(g, src) if g is not self.dist.group.WORLD else src, group=g)
         return box[0]
 
-    def _reduce_flag(self, flag: bool, op) -> bool:
-        # one int32 through all_reduce instead of a pickled object through all_gather_object: the trainer's hooks ask this
-        # every few hundred steps of 150 us, so the question has to be cheap (NCCL reduces device tensors only)
-        dev = torch.device("cuda", torch.cuda.current_device()) if self.backend == "nccl" else torch.device("cpu")
-        t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=dev)
-        self.dist.all_reduce(t, op=op, group=self.group)
+    def _reduce_flag(self, flag: bool, reduce_any: bool) -> bool:
+        # gloo: one int32 through all_reduce instead of a pickled object through all_gather_object - the trainer's hooks ask
+        # this every hundred steps of 150 us, so the question has to be cheap.  NCCL keeps the object path (it reduces device
+        # tensors only, and either form ends in a host read of the result there).
+        if self.backend != "gloo":
+            flags = self.all_gather_object(bool(flag))
+            return any(flags) if reduce_any else all(flags)
+        t = torch.tensor([1 if flag else 0], dtype=torch.int32)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if reduce_any else self.dist.ReduceOp.MIN, group=self.group)
         return bool(int(t.item()))
 
     def all_true(self, flag: bool) -> bool:
-        return self._reduce_flag(flag, self.dist.ReduceOp.MIN)
+        return self._reduce_flag(flag, False)
 
     def any_true(self, flag: bool) -> bool:
-        return self._reduce_flag(flag, self.dist.ReduceOp.MAX)
+        return self._reduce_flag(flag, True)
 
     def broadcast_tensor(self, t: torch.Tensor, src: int) -> None:
         g = self.group
