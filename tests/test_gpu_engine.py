@@ -52,12 +52,15 @@ def test_forward_backward_matches_oracle(preset):
     st = native.read_state(eng.eval_state)
     assert abs(st.loss_sum - xent) < 2e-2 * max(1.0, abs(xent))
     got = eng.gradients()
+    # The oracle rounds activations AND the stored gradients (dP2, dZ2, dH, pooled conv1 gradient) to bf16 where the kernels do.
+    # Measured on a B200 over three seeds (relative L2 / worst element relative to the tensor's largest): baseline preset
+    # <= 0.006 / 0.028; reference preset (LRN twice, a second fc layer: single ReLU gates flip between the bf16 and the fp32
+    # pre-activations) <= 0.048 / 0.115.
+    l2_tol, max_tol = (2e-2, 6e-2) if preset == "baseline" else (6e-2, 0.15)
     for k, g in grads.items():
-        # bf16 activations everywhere (and an fp32, un-quantised backward pass in the oracle): judge the gradient as a
-        # whole (relative L2 error) and bound the worst element loosely
         l2 = ((got[k].float() - g).norm() / (g.norm() + 1e-20)).item()
-        assert l2 < 6e-2, (k, l2)
-        assert _rel(got[k], g) < 0.2, (k, _rel(got[k], g))
+        assert l2 < l2_tol, (k, l2)
+        assert _rel(got[k], g) < max_tol, (k, _rel(got[k], g))
 
 
 @pytest.mark.parametrize("use_graph", [False, True])
