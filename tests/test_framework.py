@@ -595,6 +595,22 @@ def test_native_loader_batch_ring_lends_buffers(tmp_path):
     sh.close()
 
 
+def test_inference_decode_stage_keeps_order():
+    """inference.py's optional decode threads: results come back in input order whatever the completion order."""
+    import time
+
+    import inference
+
+    def slow_square(i):
+        time.sleep(0.0005 * (i % 4))
+        return i * i
+
+    for threads in (1, 4):
+        assert list(inference._ordered_parallel_map(slow_square, iter(range(150)), threads, depth=16)) == [i * i for i in range(150)]
+    with pytest.raises(ZeroDivisionError):
+        list(inference._ordered_parallel_map(lambda i: 1 // (i - 5), range(10), 3))
+
+
 def test_image_preprocessing_helpers():
     from distributed_tensorflow_ibm_mnist_b200.data import readers
 
