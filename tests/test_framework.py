@@ -123,6 +123,46 @@ def test_tf_lrn_semantics():
     assert torch.allclose(got, want, atol=1e-6)
 
 
+def test_lrn_kernel_arithmetic_in_float32():
+    """The LRN epilogues of the kernels (csrc/common/ptx.cuh: window9_sums, lrn_pow_m075) restated in numpy float32: channel
+    windows as differences of running prefix sums, s^-0.75 as r*sqrt(r) with r = s^-0.5.  Against float64 TF semantics the
+    forward value must hold to 1e-5 for ordinary activations and stay bounded by alpha * ulp(prefix) when one channel dwarfs
+    the others (the prefix then swallows the small squares - the error enters s = 1 + alpha*sum scaled by alpha = 1.1e-4)."""
+    alpha, beta = np.float32(0.001 / 9.0), 0.75
+
+    def lrn_kernel_way(a):                       # a: [pixels, C] float32
+        n, c = a.shape
+        ext = np.zeros((n, c + 8), np.float32)
+        ext[:, 4:4 + c] = a * a
+        p = np.zeros((n, c + 9), np.float32)
+        for k in range(c + 8):                   # sequential float32 additions, like the unrolled loop
+            p[:, k + 1] = p[:, k] + ext[:, k]
+        win = p[:, 9:9 + c] - p[:, 0:c]
+        s = np.float32(1.0) + alpha * win
+        r = (np.float32(1.0) / np.sqrt(s)).astype(np.float32)
+        return (a * (r * np.sqrt(r))).astype(np.float32)
+
+    def lrn_reference(a):
+        a64 = a.astype(np.float64)
+        out = np.empty_like(a64)
+        for ch in range(a.shape[1]):
+            lo, hi = max(0, ch - 4), min(a.shape[1], ch + 5)
+            out[:, ch] = a64[:, ch] / (1.0 + (0.001 / 9.0) * (a64[:, lo:hi] ** 2).sum(1)) ** beta
+        return out
+
+    rng = np.random.default_rng(0)
+    for scale in (0.1, 1.0, 30.0):
+        a = np.maximum(rng.normal(0, scale, (500, 64)), 0).astype(np.float32)
+        got, want = lrn_kernel_way(a), lrn_reference(a)
+        assert np.abs(got - want).max() <= 1e-5 * max(1.0, np.abs(want).max()), scale
+    a = np.full((4, 32), 0.01, np.float32)
+    a[:, 3] = 3000.0                             # prefix ~9e6: its ulp (1.0) swallows the 1e-4 squares that follow
+    got, want = lrn_kernel_way(a), lrn_reference(a)
+    far = slice(12, 32)                          # channels whose window does not contain the large one
+    assert np.abs(got[:, far] / want[:, far] - 1).max() < 2e-4
+    assert np.abs(got[:, :12] / want[:, :12] - 1).max() < 1e-5
+
+
 def test_loss_is_xent_plus_weight_decay_and_accuracy_rule():
     spec = presets.make_spec("reference")
     p = oracle.init_params(spec, seed=0)
