@@ -94,3 +94,25 @@ def test_example_roundtrip_and_native_parser_agrees(tmp_path_factory, image, lab
     x, y = ds.next()
     ds.close()
     assert x.numpy().tobytes() == image and int(y[0]) == int(np.int64(label).astype(np.int32))
+
+
+@settings(**SET)
+@given(st.lists(st.tuples(st.binary(min_size=24, max_size=24),
+                          st.one_of(st.integers(0, 9), st.integers(0, 127), st.integers(128, 70000), st.integers(-5, -1))),
+                min_size=2, max_size=40))
+def test_native_loader_fast_path_agrees_with_parser_on_any_label_mix(tmp_path_factory, records):
+    """Same-sized images whose labels need one, two, three or ten varint bytes, in any order: the C++ reader's remembered
+    record shape applies only where the bytes outside pixels and label value are identical; everything else must take the
+    general parser - each record is compared with what the Python codec decodes."""
+    from distributed_tensorflow_ibm_mnist_b200.data import readers
+
+    if readers._native_loader_lib() is None:
+        return
+    p = str(tmp_path_factory.mktemp("rec") / "mix.tfrecord")
+    tfrecord.write_mnist_tfrecord(p, [r[0] for r in records], [r[1] for r in records])
+    ds = readers.TFRecordBatches([p], len(records), 24, shuffle=False, native=True, prefetch_batches=0)
+    for _ in range(2):                                   # the second pass starts with a remembered shape
+        x, y = ds.next()
+        for i, (img, lab) in enumerate(records):
+            assert x[i].numpy().tobytes() == img and int(y[i]) == int(np.int64(lab).astype(np.int32)), (i, lab)
+    ds.close()
