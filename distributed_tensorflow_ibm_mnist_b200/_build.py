@@ -67,13 +67,15 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         obj = obj_dir / (str(src.relative_to(CSRC)).replace("/", "__") + ".o")
         stamp = obj.with_suffix(".stamp")
         want = _digest([src]) + hdr_digest
-        if not force and obj.exists() and stamp.exists() and stamp.read_text() == want:
-            return obj, ""
+        log = obj.with_suffix(".log")            # ptxas -v output of this object: ptxas.log stays complete when only
+        if not force and obj.exists() and stamp.exists() and stamp.read_text() == want:     # some sources are recompiled
+            return obj, log.read_text() if log.exists() else ""
         cmd = [nvcc, *NVCC_FLAGS, "-I", str(REPO / "include"), "-c", str(src), "-o", str(obj)]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
         stamp.write_text(want)
+        log.write_text(r.stderr)
         return obj, r.stderr
 
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 2)) as ex:
