@@ -814,3 +814,42 @@ def test_dist_plane_passes_file_descriptors(tmp_path):
     outs = [p.communicate(timeout=180) for p in procs]
     for r, (p, (o, e)) in enumerate(zip(procs, outs)):
         assert p.returncode == 0 and f"FD_EXCHANGE_OK {r}" in o, e[-2000:]
+
+
+def test_kernel_register_budgets_from_the_build_log():
+    """Performance invariants that live in register counts (ptxas -v output kept by the build): kernels that are designed to
+    SHARE an SM must keep fitting together, the LRN kernels must stay spill free, and no new spills may appear unnoticed."""
+    import re
+
+    log = os.path.join(ROOT, "distributed_tensorflow_ibm_mnist_b200", "_native", "ptxas.log")
+    if not os.path.exists(log):
+        pytest.skip("library not built here")
+    text = open(log).read()
+    kernels = {}
+    for m in re.finditer(r"Compiling entry function '(\w+)' for 'sm_100a'.*?(\d+) bytes spill stores, (\d+) bytes spill loads.*?Used (\d+) registers",
+                         text, flags=re.S):
+        kernels[m.group(1)] = {"spill": int(m.group(2)) + int(m.group(3)), "regs": int(m.group(4))}
+    assert len(kernels) >= 40, len(kernels)
+
+    def find(*parts):
+        hits = [k for k in kernels if all(p in k for p in parts)]
+        assert len(hits) == 1, (parts, hits)
+        return kernels[hits[0]]
+
+    def alloc(regs, threads):                  # registers are allocated per warp in units of 8 per thread
+        return -(-regs // 8) * 8 * threads
+
+    update = find("fused_update_stride_kernel")
+    dgrad, dgrad_lrn = find("conv2_dgrad_kernelILb0"), find("conv2_dgrad_kernelILb1")
+    # the early optimizer update (384 threads) runs beside conv2_dgrad (384 threads) on every SM: 64 K registers per SM
+    assert alloc(update["regs"], 384) + alloc(dgrad["regs"], 384) <= 65536
+    assert alloc(update["regs"], 384) + alloc(dgrad_lrn["regs"], 384) <= 65536
+    # two 320-thread conv1 CTAs per SM (one image channel)
+    assert 2 * alloc(find("conv1_sw_kernelILi1ELb0")["regs"], 320) <= 65536
+    # spill free: everything except the conv1 kernels' known 8-24 byte frames
+    for name, k in kernels.items():
+        if "conv1_tc_kernel" in name or "conv1_sw_kernelILi1" in name:
+            assert k["spill"] <= 80, (name, k)
+        else:
+            assert k["spill"] == 0, (name, k)
+    assert find("unpool2_lrn_kernel")["regs"] <= 64
