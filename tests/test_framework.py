@@ -853,3 +853,36 @@ def test_kernel_register_budgets_from_the_build_log():
         else:
             assert k["spill"] == 0, (name, k)
     assert find("unpool2_lrn_kernel")["regs"] <= 64
+
+
+def test_built_library_is_blackwell_native_sass():
+    """SASS of the built library (cuobjdump, no GPU needed): every GEMM-shaped kernel issues tcgen05.mma (UTC*MMA) with TMEM
+    read-back (LDTM) and bulk/TMA operand loads, nothing falls back to legacy mma.sync (HMMA), and the fused exchange
+    kernels carry multimem (NVLS) reductions."""
+    import re
+    import shutil
+    import subprocess
+
+    lib = os.path.join(ROOT, "distributed_tensorflow_ibm_mnist_b200", "_native", "libdtm_b200.so")
+    if not os.path.exists(lib) or shutil.which("cuobjdump") is None:
+        pytest.skip("library or cuobjdump not available")
+    txt = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True, timeout=300).stdout
+    parts = re.split(r"^\s*Function : (\S+)\s*$", txt, flags=re.M)
+    funcs = {parts[k]: parts[k + 1] for k in range(1, len(parts), 2)}
+    assert len(funcs) >= 40
+
+    def count(body, mnemonic):
+        return len(re.findall(r"\b" + mnemonic, body))
+
+    assert all(count(b, "HMMA") == 0 for b in funcs.values())
+    tensor = [n for n in funcs if any(t in n for t in ("gemm_bf16_kernel", "conv2_fwd_kernel", "conv2_dgrad_kernel",
+                                                       "conv_wgrad_fused_kernel", "conv1_sw_kernel", "conv2_wgrad_kernel"))]
+    assert len(tensor) >= 15
+    for n in tensor:
+        b = funcs[n]
+        assert count(b, "UTC[A-Z]*MMA") > 0 and count(b, "LDTM") > 0, n
+        assert count(b, "UBLKCP") + count(b, "UTMALDG") + count(b, "STS") > 0, n
+    assert all(count(funcs[n], "UTMALDG") > 0 for n in funcs if "gemm_bf16_kernel" in n)          # TMA tensor maps
+    assert all(count(funcs[n], "UBLKCP") > 0 for n in funcs if "conv2_fwd_kernel" in n or "conv_wgrad_fused" in n)
+    nvls = [n for n in funcs if "fused_allreduce_update_kernelILb1" in n or "allreduce_kernel" in n]
+    assert nvls and all(count(funcs[n], "LDGMC") > 0 for n in nvls if "fused_allreduce_update_kernelILb1" in n)
