@@ -886,3 +886,14 @@ def test_built_library_is_blackwell_native_sass():
     assert all(count(funcs[n], "UBLKCP") > 0 for n in funcs if "conv2_fwd_kernel" in n or "conv_wgrad_fused" in n)
     nvls = [n for n in funcs if "fused_allreduce_update_kernelILb1" in n or "allreduce_kernel" in n]
     assert nvls and all(count(funcs[n], "LDGMC") > 0 for n in nvls if "fused_allreduce_update_kernelILb1" in n)
+
+
+def test_no_cluster_multicast_loads_in_peer_memory_kernels():
+    """TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung
+    the GPU: the communication kernels (the only code that holds peer pointers) contain no cluster-multicast bulk load."""
+    import re
+
+    comm = os.path.join(ROOT, "csrc", "comm")
+    for name in sorted(os.listdir(comm)):
+        text = open(os.path.join(comm, name)).read()
+        assert not re.search(r"cp\.async\.bulk[\w.:]*\.multicast::cluster", text), name
