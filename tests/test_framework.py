@@ -897,3 +897,45 @@ def test_no_cluster_multicast_loads_in_peer_memory_kernels():
     for name in sorted(os.listdir(comm)):
         text = open(os.path.join(comm, name)).read()
         assert not re.search(r"cp\.async\.bulk[\w.:]*\.multicast::cluster", text), name
+
+
+def test_c_abi_header_library_and_bindings_agree():
+    """include/dtm_b200.h is the contract: every function it declares is exported by the built library, and every ctypes
+    signature the Python bindings register has the header's parameter count (the mismatch ctypes cannot detect itself)."""
+    import ctypes
+    import re
+
+    from distributed_tensorflow_ibm_mnist_b200.ops import _lib
+
+    if not _lib.available():
+        pytest.skip("library not built here")
+    text = open(os.path.join(ROOT, "include", "dtm_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
+    text = re.sub(r"//[^\n]*", " ", text)
+    decls = {}
+    for m in re.finditer(r"\b(dtm_\w+)\s*\(([^()]*)\)\s*;", text):
+        args = m.group(2).strip()
+        decls[m.group(1)] = 0 if args in ("", "void") else args.count(",") + 1
+    assert len(decls) >= 50 and decls["dtm_abi_version"] == 0 and decls["dtm_loader_ring_start"] == 4
+    assert int(re.search(r"#define DTM_ABI_VERSION (\d+)", open(os.path.join(ROOT, "include", "dtm_b200.h")).read()).group(1)) == _lib.ABI_VERSION
+    lib = ctypes.CDLL(str(_lib.lib_path()))
+    missing = [n for n in decls if not hasattr(lib, n)]
+    assert not missing, missing
+    # importing the op modules registers their signatures
+    from distributed_tensorflow_ibm_mnist_b200.data import readers
+    from distributed_tensorflow_ibm_mnist_b200.ops import native  # noqa: F401
+    from distributed_tensorflow_ibm_mnist_b200.parallel import peer_comm  # noqa: F401
+
+    readers._native_loader_lib()
+    assert len(_lib.EXTRA_SIGNATURES) >= 30
+    for name, (argtypes, _res) in _lib.EXTRA_SIGNATURES.items():
+        assert name in decls, f"{name} is bound from Python but not declared in dtm_b200.h"
+        assert len(argtypes) == decls[name], (name, len(argtypes), decls[name])
+    loaded = _lib.load()                     # ... and whatever else the loader itself declares (gemm, probe, device info)
+    bound = 0
+    for name, n_args in decls.items():
+        fn = getattr(loaded, name)
+        if fn.argtypes is not None:
+            bound += 1
+            assert len(fn.argtypes) == n_args, (name, len(fn.argtypes), n_args)
+    assert bound >= 35
