@@ -939,3 +939,36 @@ def test_c_abi_header_library_and_bindings_agree():
             bound += 1
             assert len(fn.argtypes) == n_args, (name, len(fn.argtypes), n_args)
     assert bound >= 35
+
+
+def test_ctypes_struct_mirrors_match_the_c_header(tmp_path):
+    """dtm_train_state / dtm_update_config cross the ABI by value and by device copy: the ctypes mirrors in ops/native.py must
+    have the C compiler's size and field offsets (a plain-C translation unit including the header also proves the header is C)."""
+    import ctypes
+    import shutil
+    import subprocess
+
+    from distributed_tensorflow_ibm_mnist_b200.ops import native
+
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    fields_state = ["global_step", "nan_flag", "ticket", "last_xent", "wl_sum", "last_wl", "loss_avg", "work"]
+    fields_cfg = ["optimizer", "decay_steps", "base_lr", "ema_decay", "seg_offset", "seg_wd", "seg_zero_grad", "seg_gather_bf16",
+                  "pack_seg", "pack_fwd", "pack_dgrad"]
+    src = tmp_path / "layout.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "dtm_b200.h"\nint main(void) {\n'
+                   '  printf("%zu %zu", sizeof(dtm_train_state), sizeof(dtm_update_config));\n'
+                   + "".join(f'  printf(" %zu", offsetof(dtm_train_state, {f}));\n' for f in fields_state)
+                   + "".join(f'  printf(" %zu", offsetof(dtm_update_config, {f}));\n' for f in fields_cfg)
+                   + "  return 0;\n}\n")
+    exe = tmp_path / "layout"
+    r = subprocess.run([cc, "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True).stdout.split()]
+    want = [ctypes.sizeof(native.TrainState), ctypes.sizeof(native.UpdateConfig)]
+    want += [getattr(native.TrainState, f).offset for f in fields_state]
+    want += [getattr(native.UpdateConfig, f).offset for f in fields_cfg]
+    assert got == want, (got, want)
+    assert native.STATE_BYTES == got[0]
