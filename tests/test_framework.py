@@ -972,3 +972,59 @@ def test_ctypes_struct_mirrors_match_the_c_header(tmp_path):
     want += [getattr(native.UpdateConfig, f).offset for f in fields_cfg]
     assert got == want, (got, want)
     assert native.STATE_BYTES == got[0]
+
+
+def test_plain_c_host_uses_the_library(tmp_path):
+    """INTEGRATION.md's claim that the library is usable from a plain-C host: a C99 program built against include/dtm_b200.h
+    checks the ABI version, computes a CRC-32C and reads batches from a TFRecord file through the loader and its batch ring -
+    no Python, no GPU."""
+    import shutil
+    import subprocess
+
+    from distributed_tensorflow_ibm_mnist_b200.formats import tfrecord
+    from distributed_tensorflow_ibm_mnist_b200.ops import _lib
+
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None or not _lib.available():
+        pytest.skip("no C compiler or library not built")
+    rec = str(tmp_path / "d.tfrecord")
+    tfrecord.write_mnist_tfrecord(rec, [bytes([i]) * 784 for i in range(64)], [i % 10 for i in range(64)])
+    src = tmp_path / "host.c"
+    src.write_text(r'''
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include "dtm_b200.h"
+int main(int argc, char** argv) {
+  if (dtm_abi_version() != DTM_ABI_VERSION) { printf("abi %d\n", dtm_abi_version()); return 1; }
+  if (dtm_crc32c("123456789", 9, 0) != 0xE3069283u) return 2;
+  const char* files[1] = {argv[1]};
+  void* ld = dtm_loader_create(files, 1, 16, 784, 2, 7, /*shuffle=*/0, 0);
+  if (!ld) { printf("create: %s\n", dtm_last_error()); return 3; }
+  uint8_t* px = malloc(16 * 784); int32_t lab[16];
+  if (dtm_loader_next(ld, px, lab) != 0) return 4;
+  for (int i = 0; i < 16; ++i) if (px[i * 784] != i || lab[i] != i % 10) return 5;
+  enum { NB = 3, BYTES = 16 * 784 + 16 * 4 };
+  uint8_t* bufs[NB];
+  for (int i = 0; i < NB; ++i) bufs[i] = malloc(BYTES);
+  if (dtm_loader_ring_start(ld, bufs, NB, 16 * 784) != 0) { printf("ring: %s\n", dtm_last_error()); return 6; }
+  for (int b = 1; b < 8; ++b) {                     /* batches 1..7: records 16 b .. 16 b + 15, wrapping after 64 */
+    int idx = dtm_loader_ring_acquire(ld);
+    if (idx < 0) return 7;
+    const int32_t* l = (const int32_t*)(bufs[idx] + 16 * 784);
+    for (int i = 0; i < 16; ++i) { int r = (16 * b + i) % 64; if (bufs[idx][i * 784] != r || l[i] != r % 10) return 8; }
+    if (dtm_loader_ring_release(ld, idx) != 0) return 9;
+  }
+  if (dtm_loader_next(ld, px, lab) == 0 || !strstr(dtm_last_error(), "ring")) return 10;
+  printf("records_read>=%d ok\n", (int)(dtm_loader_records_read(ld) >= 128));
+  dtm_loader_destroy(ld);
+  return 0;
+}
+''')
+    exe = tmp_path / "host"
+    libdir = str(_lib.lib_path().parent)
+    r = subprocess.run([cc, "-std=c99", "-Wall", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src), "-L", libdir,
+                        "-ldtm_b200", f"-Wl,-rpath,{libdir}"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(exe), rec], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "records_read>=1 ok" in r.stdout, (r.returncode, r.stdout, r.stderr)
