@@ -1,5 +1,6 @@
-// conv1 weight gradient on CUDA cores (default; conv1_wgrad_tc.cu is the opt-in tensor-core variant, the forward pass lives
-// in conv1_tc.cu).
+// conv1 weight gradient on CUDA cores: the round-1 kernel, kept as the `DTM_WGRAD_FUSED=0` arm (the default is the fused
+// tensor-core kernel in conv_wgrad_fused.cu; conv1_wgrad_tc.cu is a second opt-in variant; the forward pass lives in
+// conv1_sw.cu / conv1_tc.cu).
 //
 // Weight gradient (autodiff of the same lines; conv1 has no input gradient): the pooled gradient is routed
 // through the saved arg-max to one of four positions, so each (pooled pixel, channel) contributes exactly one
@@ -16,11 +17,6 @@ constexpr int C1_OUT = 32;
 constexpr int IN_HW = 28;
 constexpr int IN_PITCH = 34;  // 28 + 2*2 halo, +2 so the four pooling positions hit distinct banks
 constexpr int IN_ROWS = 32;
-
-constexpr float LRN_BIAS = 1.0f;
-constexpr float LRN_ALPHA = 0.001f / 9.0f;
-constexpr float LRN_BETA = 0.75f;
-constexpr int LRN_RADIUS = 4;
 
 template <int CIN>
 DTM_DEVICE void load_image_to_smem(float* s_in, const void* x, int in_is_float, int img) {
