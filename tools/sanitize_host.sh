@@ -1,6 +1,6 @@
 #!/bin/bash
 # Host-side sanitizer passes over the C++ input pipeline (the GPU pool refuses compute-sanitizer; this part needs no GPU):
-#   tools/sanitize_host.sh [out_dir]     -> <out_dir>/sanitize_host_tsan_r2.log, sanitize_host_asan_ubsan_r2.log
+#   tools/sanitize_host.sh [out_dir]     -> <out_dir>/sanitize_host_{tsan,asan_ubsan,fuzz}_r2.log
 # Builds tools/loader_stress.cpp together with csrc/io/{record_loader,crc32c}.cpp under -fsanitize=thread and under
 # -fsanitize=address,undefined, writes an MNIST-shaped TFRecord file and runs the stress driver on it.
 set -u
@@ -39,5 +39,21 @@ for mode in tsan asan_ubsan; do
   } > "$LOG" 2>&1
   tail -3 "$LOG"
 done
+# third pass: parser fuzz under ASan + UBSan (every input in an exact-size heap buffer)
+LOG="$OUT/sanitize_host_fuzz_r2.log"
+{
+  echo "== g++ -std=c++17 -O1 -g -fsanitize=address,undefined parse_fuzz.cpp crc32c.cpp"
+  g++ -std=c++17 -O1 -g -fsanitize=address,undefined -fno-sanitize-recover=undefined $INC -o "$TMP/fuzz" "$ROOT/tools/parse_fuzz.cpp" \
+      "$ROOT/csrc/io/crc32c.cpp" -lpthread 2>&1 | grep -v "warning:"
+  if [ -x "$TMP/fuzz" ]; then
+    ASAN_OPTIONS="detect_leaks=1 exitcode=67" "$TMP/fuzz" 300000 2>&1
+    code=$?
+    echo "== exit code $code ($([ $code -eq 0 ] && echo 'no reports' || echo 'REPORTS ABOVE'))"
+    [ $code -ne 0 ] && rc=1
+  else
+    echo "== build failed"; rc=2
+  fi
+} > "$LOG" 2>&1
+tail -2 "$LOG"
 rm -rf "$TMP"
 exit $rc
