@@ -1028,3 +1028,37 @@ int main(int argc, char** argv) {
     assert r.returncode == 0, r.stderr
     r = subprocess.run([str(exe), rec], capture_output=True, text=True, timeout=60)
     assert r.returncode == 0 and "records_read>=1 ok" in r.stdout, (r.returncode, r.stdout, r.stderr)
+
+
+def test_native_loader_reports_damaged_and_empty_files(tmp_path):
+    """Error paths of the C++ reader over mapped files: truncated header, truncated payload, corrupt length, empty input."""
+    from distributed_tensorflow_ibm_mnist_b200.data import readers
+    from distributed_tensorflow_ibm_mnist_b200.formats import tfrecord
+
+    if readers._native_loader_lib() is None:
+        pytest.skip("libdtm_b200.so not built")
+    good = str(tmp_path / "good.tfrecord")
+    tfrecord.write_mnist_tfrecord(good, [bytes([i]) * 784 for i in range(40)], [i % 10 for i in range(40)])
+    raw = open(good, "rb").read()
+    rec_len = len(raw) // 40
+
+    def first_error(data, batch=8):
+        p = str(tmp_path / "bad.tfrecord")
+        open(p, "wb").write(data)
+        ds = readers.TFRecordBatches([p], batch, 784, shuffle=False, native=True, prefetch_batches=0)
+        try:
+            for _ in range(12):
+                ds.next()
+        except ValueError as e:
+            return str(e)
+        finally:
+            ds.close()
+        return ""
+
+    assert "truncated TFRecord header" in first_error(raw[:rec_len * 20 + 5])
+    assert "truncated TFRecord in" in first_error(raw[:rec_len * 20 + 100])
+    damaged = bytearray(raw)
+    damaged[rec_len * 3 + 2] ^= 0x01                                        # inside the 4th record's length field
+    assert "corrupt TFRecord length" in first_error(bytes(damaged))
+    assert "no records" in first_error(b"")
+    assert first_error(raw) == ""                                            # the undamaged file streams on across epochs
