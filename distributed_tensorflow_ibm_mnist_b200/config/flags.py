@@ -146,6 +146,13 @@ def DEFINE_alias(alias: str, target: str) -> None:  # noqa: N802
 
 def run(main: Callable, argv: list[str] | None = None) -> None:
     """``tf.app.run`` stand-in: parse flags, call ``main(remaining_argv)``, exit with its return value."""
+    args = list(sys.argv[1:] if argv is None else argv)
+    flag_part = args[:args.index("--")] if "--" in args else args
+    if any(a in ("--help", "-h", "-help", "--helpshort", "--helpfull") for a in flag_part):
+        # tf.app.run prints the program's flags and exits (status 1 in TF-1.x; 0 here, like every other tool)
+        doc = (getattr(sys.modules.get("__main__"), "__doc__", None) or "").strip()
+        print((doc + "\n\n" if doc else "") + f"flags:\n{FLAGS.usage()}")
+        sys.exit(0)
     try:
         rest = FLAGS.parse(argv)
     except FlagError as e:

@@ -48,6 +48,18 @@ def test_flags_tf_style_syntax():
     assert fv.task_id == 0
 
 
+def test_entry_points_print_their_flags_on_help():
+    """tf.app.run's --help: the program's docstring and flags, exit status 0; an unknown flag is still an error (status 2)."""
+    import subprocess
+
+    for script, flag in (("main.py", "--input_threads"), ("inference.py", "--prob_thresh")):
+        for h in ("--help", "-h"):
+            r = subprocess.run([sys.executable, script, h], cwd=ROOT, capture_output=True, text=True, timeout=120)
+            assert r.returncode == 0 and "flags:" in r.stdout and flag in r.stdout and "flag error" not in r.stderr, (script, h)
+    r = subprocess.run([sys.executable, "main.py", "--no_such_flag=1"], cwd=ROOT, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 2 and "unknown flag --no_such_flag" in r.stderr
+
+
 # ---- parameter manager -------------------------------------------------------------------------------------
 def test_parameter_manager_getters_and_file(tmp_path):
     pm.reset()
